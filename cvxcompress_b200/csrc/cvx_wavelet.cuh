@@ -1,0 +1,298 @@
+// cvx_wavelet.cuh -- 1-D multi-level Antonini/CDF 9/7 line transforms.
+//
+// Two arithmetic variants of the same operator:
+//   EXACT : direct-form 9/7-tap filter bank in exactly the association the reference ships
+//           (generated _Ds79_AVX_n / _Us79_AVX_n, emitted by Wavelet_Transform_Slow.cpp:416-448,
+//           :465-490, :613-638, :664-696): acc = a4*p4; acc = acc + a3*p3; ... ; acc = acc + a0*t0,
+//           separate fp32 mul and add (the reference makefile:6-8 builds with -mavx only => no FMA).
+//           Bit-identical to Wavelet_Transform_Fast_{Forward,Inverse}.
+//   LIFT  : the 4-step lifting factorisation (+ two scalings) of the same filter bank with FMA,
+//           in place on an interleaved line.  Equal to the filter bank to 2e-14 in fp64
+//           (checked for n = 2..256); ~4e-7 rms-relative in fp32.
+//
+// Lines of <= 64 samples live in registers (all indices are compile-time after unrolling).
+// Mirror rules: MIRR / MIRR_SL / MIRR_SH, Wavelet_Transform_Slow.cpp:59-67, :178-199.
+#pragma once
+#include <cuda_runtime.h>
+
+#ifndef CVX_HD
+#define CVX_HD __host__ __device__ __forceinline__
+#endif
+
+#ifdef __CUDA_ARCH__
+#define CVX_MUL(a, b) __fmul_rn((a), (b))
+#define CVX_ADD(a, b) __fadd_rn((a), (b))
+#define CVX_FMA(a, b, c) __fmaf_rn((a), (b), (c))
+#else
+#include <cmath>
+// host build uses -ffp-contract=off, so these stay separate roundings
+#define CVX_MUL(a, b) ((a) * (b))
+#define CVX_ADD(a, b) ((a) + (b))
+#define CVX_FMA(a, b, c) fmaf((a), (b), (c))
+#endif
+
+namespace cvx {
+
+// analysis / synthesis taps, Wavelet_Transform_Slow.cpp:21-30 and :136-145
+#define CVX_AL0 8.526986790094000e-001f
+#define CVX_AL1 3.774028556126500e-001f
+#define CVX_AL2 -1.106244044184200e-001f
+#define CVX_AL3 -2.384946501938001e-002f
+#define CVX_AL4 3.782845550699501e-002f
+#define CVX_AH0 7.884856164056601e-001f
+#define CVX_AH1 -4.180922732222101e-001f
+#define CVX_AH2 -4.068941760955800e-002f
+#define CVX_AH3 6.453888262893799e-002f
+#define CVX_SL0 7.884856164056601e-001f
+#define CVX_SL1 4.180922732222101e-001f
+#define CVX_SL2 -4.068941760955800e-002f
+#define CVX_SL3 -6.453888262893799e-002f
+#define CVX_SH0 8.526986790094000e-001f
+#define CVX_SH1 -3.774028556126500e-001f
+#define CVX_SH2 -1.106244044184200e-001f
+#define CVX_SH3 2.384946501938001e-002f
+#define CVX_SH4 3.782845550699501e-002f
+
+// lifting constants (Daubechies-Sweldens factorisation of the 9/7 pair) and the two
+// scalings that reproduce the reference's sqrt(2)-normalised taps.
+#define CVX_LA -1.586134342059924f
+#define CVX_LB -0.052980118572961f
+#define CVX_LG 0.882911075530934f
+#define CVX_LD 0.443506852043971f
+#define CVX_ZL 1.1496043988602411f
+#define CVX_ZH 0.8698644516247813f
+#define CVX_IZL 0.8698644516247813f /* 1/ZL == ZH for this normalisation */
+#define CVX_IZH 1.1496043988602411f /* 1/ZH == ZL */
+
+CVX_HD constexpr int mirr(int v, int n)
+{
+    v = v < 0 ? -v : v;
+    v = v >= n ? 2 * n - 2 - v : v;
+    v = v < 0 ? -v : v;
+    v = v >= n ? 2 * n - 2 - v : v;
+    return v;
+}
+CVX_HD constexpr int mirr_sl(int v, int nl)
+{
+    v = v < 0 ? -v : v; v = v >= nl ? 2 * nl - 1 - v : v;
+    v = v < 0 ? -v : v; v = v >= nl ? 2 * nl - 1 - v : v;
+    v = v < 0 ? -v : v; v = v >= nl ? 2 * nl - 1 - v : v;
+    return v;
+}
+CVX_HD constexpr int mirr_sh(int v, int nl, int nh)
+{
+    v -= nl;
+    v = v < 0 ? -v - 1 : v; v = v >= nh ? 2 * nh - 2 - v : v;
+    v = v < 0 ? -v - 1 : v; v = v >= nh ? 2 * nh - 2 - v : v;
+    v = v < 0 ? -v - 1 : v; v = v >= nh ? 2 * nh - 2 - v : v;
+    return nl + v;
+}
+
+// ------------------------------------------------------------------------------------------
+// EXACT, register-resident.  One level on v[0..N): low half then high half (out-of-place
+// semantics through the copy t[]).
+// ------------------------------------------------------------------------------------------
+template <int N>
+CVX_HD void fwd_exact_level(float* v)
+{
+    float t[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) t[i] = v[i];
+    constexpr int nh = N / 2;
+#pragma unroll
+    for (int ix = 0; ix < nh; ++ix) {
+        {
+            const int i0 = 2 * ix;
+            float acc = CVX_MUL(CVX_AL4, CVX_ADD(t[mirr(i0 - 4, N)], t[mirr(i0 + 4, N)]));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AL3, CVX_ADD(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AL2, CVX_ADD(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AL1, CVX_ADD(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AL0, t[i0]));
+            v[ix] = acc;
+        }
+        {
+            const int i0 = 2 * ix + 1;
+            float acc = CVX_MUL(CVX_AH3, CVX_ADD(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)]));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AH2, CVX_ADD(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AH1, CVX_ADD(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_AH0, t[i0]));
+            v[nh + ix] = acc;
+        }
+    }
+}
+
+template <int N>
+CVX_HD void inv_exact_level(float* v)
+{
+    float t[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) t[i] = v[i];
+    constexpr int nh = N / 2, nl = N - nh;
+#pragma unroll
+    for (int k = 0; k < nl; ++k) {
+        {   // even sample 2k
+            float acc = CVX_MUL(CVX_SH3, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)]));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SL2, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 1, nl)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SH1, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k, nl, nh)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SL0, t[k]));
+            v[2 * k] = acc;
+        }
+        {   // odd sample 2k+1
+            float acc = CVX_MUL(CVX_SH4, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 2, nl, nh)]));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SL3, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 2, nl)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SH2, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SL1, CVX_ADD(t[mirr_sl(k, nl)], t[mirr_sl(k + 1, nl)])));
+            acc = CVX_ADD(acc, CVX_MUL(CVX_SH0, t[nl + k]));
+            v[2 * k + 1] = acc;
+        }
+    }
+}
+
+// levels N, N/2, ..., 2 (Wavelet_Transform_Fast.cpp:48-55) / 2, ..., N (:183-190)
+template <int N>
+CVX_HD void fwd_exact(float* v)
+{
+    fwd_exact_level<N>(v);
+    if constexpr (N > 2) fwd_exact<N / 2>(v);
+}
+template <int N>
+CVX_HD void inv_exact(float* v)
+{
+    if constexpr (N > 2) inv_exact<N / 2>(v);
+    inv_exact_level<N>(v);
+}
+
+// ------------------------------------------------------------------------------------------
+// LIFT, register-resident, in place on the interleaved line.  Level with stride S works on
+// the samples at positions S*j, j < N/S; evens are s_j, odds are d_j.  Boundary:
+// s_{m} -> s_{m-1}, d_{-1} -> d_0 (whole-sample symmetric extension == MIRR).
+// ------------------------------------------------------------------------------------------
+template <int N, int S>
+CVX_HD void fwd_lift_level(float* v)
+{
+    constexpr int m = N / S / 2;
+#define CVX_S(j) v[S * 2 * (j)]
+#define CVX_D(j) v[S * (2 * (j) + 1)]
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(CVX_LA, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(CVX_LB, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(CVX_LG, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(CVX_LD, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) { CVX_S(j) = CVX_MUL(CVX_S(j), CVX_ZL); CVX_D(j) = CVX_MUL(CVX_D(j), CVX_ZH); }
+}
+template <int N, int S>
+CVX_HD void inv_lift_level(float* v)
+{
+    constexpr int m = N / S / 2;
+#pragma unroll
+    for (int j = 0; j < m; ++j) { CVX_S(j) = CVX_MUL(CVX_S(j), CVX_IZL); CVX_D(j) = CVX_MUL(CVX_D(j), CVX_IZH); }
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(-CVX_LD, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(-CVX_LG, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(-CVX_LB, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+#pragma unroll
+    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(-CVX_LA, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+#undef CVX_S
+#undef CVX_D
+}
+template <int N, int S = 1>
+CVX_HD void fwd_lift(float* v)
+{
+    fwd_lift_level<N, S>(v);
+    if constexpr (N / S > 2) fwd_lift<N, S * 2>(v);
+}
+template <int N, int S = 1>
+CVX_HD void inv_lift(float* v)
+{
+    if constexpr (N / S > 2) inv_lift<N, S * 2>(v);
+    inv_lift_level<N, S>(v);
+}
+
+// interleaved position p  <->  sub-band index (low first, recursively; DC at 0)
+CVX_HD constexpr int lift_pos_to_idx(int p, int N)
+{
+    if (p == 0) return 0;
+    int s = p & (-p);
+    return N / (2 * s) + (p / s - 1) / 2;
+}
+
+// ------------------------------------------------------------------------------------------
+// Uniform front end.  v[] holds the line in NATURAL order before fwd / after inv, and in
+// SUB-BAND order after fwd / before inv for EXACT; for LIFT the sub-band side is addressed
+// through sub_pos<>(i): the register that holds sub-band coefficient i.
+// ------------------------------------------------------------------------------------------
+template <int N, bool EXACT>
+CVX_HD void fwd_line(float* v)
+{
+    if constexpr (EXACT) fwd_exact<N>(v); else fwd_lift<N>(v);
+}
+template <int N, bool EXACT>
+CVX_HD void inv_line(float* v)
+{
+    if constexpr (EXACT) inv_exact<N>(v); else inv_lift<N>(v);
+}
+// register index r -> sub-band index held there
+template <int N, bool EXACT>
+CVX_HD constexpr int reg_to_sub(int r)
+{
+    return EXACT ? r : lift_pos_to_idx(r, N);
+}
+
+// ------------------------------------------------------------------------------------------
+// Generic-length EXACT transforms on a strided line in memory with a caller-provided
+// temporary of n floats (any power of two up to 256).  Used by the staged large-block path.
+// ------------------------------------------------------------------------------------------
+__host__ __device__ inline void fwd_exact_level_mem(float* p, long stride, float* t, int n)
+{
+    for (int i = 0; i < n; ++i) t[i] = p[i * stride];
+    int nh = n / 2;
+    for (int ix = 0; ix < nh; ++ix) {
+        int i0 = 2 * ix;
+        float acc = CVX_MUL(CVX_AL4, CVX_ADD(t[mirr(i0 - 4, n)], t[mirr(i0 + 4, n)]));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AL3, CVX_ADD(t[mirr(i0 - 3, n)], t[mirr(i0 + 3, n)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AL2, CVX_ADD(t[mirr(i0 - 2, n)], t[mirr(i0 + 2, n)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AL1, CVX_ADD(t[mirr(i0 - 1, n)], t[mirr(i0 + 1, n)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AL0, t[i0]));
+        p[ix * stride] = acc;
+        i0 = 2 * ix + 1;
+        acc = CVX_MUL(CVX_AH3, CVX_ADD(t[mirr(i0 - 3, n)], t[mirr(i0 + 3, n)]));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AH2, CVX_ADD(t[mirr(i0 - 2, n)], t[mirr(i0 + 2, n)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AH1, CVX_ADD(t[mirr(i0 - 1, n)], t[mirr(i0 + 1, n)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_AH0, t[i0]));
+        p[(nh + ix) * stride] = acc;
+    }
+}
+__host__ __device__ inline void inv_exact_level_mem(float* p, long stride, float* t, int n)
+{
+    for (int i = 0; i < n; ++i) t[i] = p[i * stride];
+    int nh = n / 2, nl = n - nh;
+    for (int k = 0; k < nl; ++k) {
+        float acc = CVX_MUL(CVX_SH3, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)]));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SL2, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 1, nl)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SH1, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k, nl, nh)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SL0, t[k]));
+        p[(2 * k) * stride] = acc;
+        acc = CVX_MUL(CVX_SH4, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 2, nl, nh)]));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SL3, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 2, nl)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SH2, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SL1, CVX_ADD(t[mirr_sl(k, nl)], t[mirr_sl(k + 1, nl)])));
+        acc = CVX_ADD(acc, CVX_MUL(CVX_SH0, t[nl + k]));
+        p[(2 * k + 1) * stride] = acc;
+    }
+}
+__host__ __device__ inline void fwd_exact_mem(float* p, long stride, float* t, int dim)
+{
+    for (int n = dim; n >= 2; n >>= 1) fwd_exact_level_mem(p, stride, t, n);
+}
+__host__ __device__ inline void inv_exact_mem(float* p, long stride, float* t, int dim)
+{
+    for (int n = 2; n <= dim; n <<= 1) inv_exact_level_mem(p, stride, t, n);
+}
+
+}  // namespace cvx
