@@ -1,0 +1,493 @@
+// cvx_api.cpp -- the C ABI of include/cvx_gpu.h: argument checks, workspace, stream layout
+// (header / offset table / mulfac table / payload, CvxCompress.cpp:284-315 and :473-517) and the
+// host-pointer staging used by the CvxCompress class.  All arithmetic is in cvx_kernels.cu;
+// there is no CPU implementation of any stage here.
+#include "../../include/cvx_gpu.h"
+#include "cvx_internal.h"
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+using namespace cvx;
+
+// ---- errors -------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) return fail(CVXGPU_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+extern "C" const char* cvxgpu_last_error(void) { return g_err; }
+
+extern "C" int cvxgpu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ---- transform mode -------------------------------------------------------------------------
+static std::atomic<int> g_transform{-1};
+
+extern "C" int cvxgpu_get_transform(void)
+{
+    int m = g_transform.load();
+    if (m < 0) {
+        const char* e = getenv("CVX_GPU_TRANSFORM");
+        m = (e && (!strcmp(e, "lifting") || !strcmp(e, "lift") || !strcmp(e, "1"))) ? CVXGPU_TRANSFORM_LIFTING
+                                                                                  : CVXGPU_TRANSFORM_EXACT;
+        g_transform.store(m);
+    }
+    return m;
+}
+extern "C" int cvxgpu_set_transform(int mode)
+{
+    if (mode != CVXGPU_TRANSFORM_EXACT && mode != CVXGPU_TRANSFORM_LIFTING) return fail(CVXGPU_ERR_ARG, "unknown transform mode %d", mode);
+    g_transform.store(mode);
+    return CVXGPU_OK;
+}
+static int exact_mode() { return cvxgpu_get_transform() == CVXGPU_TRANSFORM_EXACT ? 1 : 0; }
+
+// ---- workspace ------------------------------------------------------------------------------
+extern "C" int cvxgpu_workspace_create(cvxgpu_workspace** out)
+{
+    if (!out) return fail(CVXGPU_ERR_ARG, "null workspace pointer");
+    *out = nullptr;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    cvxgpu_workspace* ws = new cvxgpu_workspace();
+    ws->device = dev;
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, dev);
+    if (e != cudaSuccess) { delete ws; return fail(CVXGPU_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
+    ws->sm_count = prop.multiProcessorCount;
+    ws->n_partial = ws->sm_count * 8;
+    if ((e = cudaMalloc(&ws->d_scalars, 256)) != cudaSuccess || (e = cudaMemset(ws->d_scalars, 0, 256)) != cudaSuccess ||
+        (e = cudaMalloc(&ws->d_partial, sizeof(double) * ws->n_partial)) != cudaSuccess ||
+        (e = cudaMallocHost(&ws->h_pinned, 256)) != cudaSuccess) {
+        cvxgpu_workspace_destroy(ws);
+        return fail(CVXGPU_ERR_CUDA, "workspace allocation: %s", cudaGetErrorString(e));
+    }
+    ws->d_sumsq = reinterpret_cast<double*>(ws->d_scalars);
+    ws->d_mulfac = reinterpret_cast<float*>(ws->d_scalars + 8);
+    ws->d_ticket = reinterpret_cast<unsigned int*>(ws->d_scalars + 16);
+    ws->d_payload_bytes = reinterpret_cast<long*>(ws->d_scalars + 24);
+    ws->d_length = reinterpret_cast<long*>(ws->d_scalars + 32);
+    ws->d_err = reinterpret_cast<int*>(ws->d_scalars + 40);
+    *out = ws;
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_workspace_destroy(cvxgpu_workspace* ws)
+{
+    if (!ws) return CVXGPU_OK;
+    if (ws->d_scalars) cudaFree(ws->d_scalars);
+    if (ws->d_partial) cudaFree(ws->d_partial);
+    if (ws->d_status) cudaFree(ws->d_status);
+    if (ws->d_scratch) cudaFree(ws->d_scratch);
+    if (ws->h_pinned) cudaFreeHost(ws->h_pinned);
+    if (ws->d_stage_vol) cudaFree(ws->d_stage_vol);
+    if (ws->d_stage_stream) cudaFree(ws->d_stage_stream);
+    if (ws->h_stage) cudaFreeHost(ws->h_stage);
+    delete ws;
+    return CVXGPU_OK;
+}
+
+// per-host-thread default workspaces, one per device
+struct TlsWorkspaces {
+    cvxgpu_workspace* ws[64] = {nullptr};
+    ~TlsWorkspaces()
+    {
+        // the CUDA context may already be gone at thread/process exit: leak device memory, free nothing
+    }
+};
+static thread_local TlsWorkspaces g_tls;
+
+static int get_ws(cvxgpu_workspace* in, cvxgpu_workspace** out)
+{
+    if (in) { *out = in; return CVXGPU_OK; }
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(CVXGPU_ERR_ARG, "device index %d out of range", dev);
+    if (!g_tls.ws[dev]) {
+        int rc = cvxgpu_workspace_create(&g_tls.ws[dev]);
+        if (rc != CVXGPU_OK) return rc;
+    }
+    *out = g_tls.ws[dev];
+    return CVXGPU_OK;
+}
+
+// ---- shape helpers --------------------------------------------------------------------------
+extern "C" int cvxgpu_is_valid_block_size(int bx, int by, int bz) { return valid_block_size(bx, by, bz) ? 1 : 0; }
+
+extern "C" long cvxgpu_num_blocks(int nx, int ny, int nz, int bx, int by, int bz)
+{
+    if (nx <= 0 || ny <= 0 || nz <= 0 || !valid_block_size(bx, by, bz)) return -1;
+    return make_shape(nx, ny, nz, bx, by, bz).nblk;
+}
+
+extern "C" long cvxgpu_max_compressed_bytes(int nx, int ny, int nz, int bx, int by, int bz, int use_local_rms)
+{
+    long nnn = cvxgpu_num_blocks(nx, ny, nz, bx, by, bz);
+    if (nnn < 0) return -1;
+    return 32 + 8 * nnn + (use_local_rms ? 4 * nnn : 0) + 4L * bx * by * bz * nnn + 7;
+}
+
+static int check_dims(int nx, int ny, int nz, int bx, int by, int bz)
+{
+    if (nx <= 0 || ny <= 0 || nz <= 0) return fail(CVXGPU_ERR_ARG, "volume dimensions must be positive (got %d x %d x %d)", nx, ny, nz);
+    if (!valid_block_size(bx, by, bz))
+        return fail(CVXGPU_ERR_ARG, "invalid block size %d x %d x %d (powers of two in 8..256; bz may be 1)", bx, by, bz);
+    return CVXGPU_OK;
+}
+
+// ---- pieces ---------------------------------------------------------------------------------
+extern "C" int cvxgpu_sumsq_device(cvxgpu_workspace* wsin, const float* d_vol, long ncells, double* d_sumsq, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    if (!d_vol || !d_sumsq || ncells <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_sumsq_device: bad argument");
+    CU(launch_sumsq(ws, d_vol, ncells, d_sumsq, (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_write_header_device(void* d_stream, int nx, int ny, int nz, int bx, int by, int bz, float scale,
+                                          int use_local_rms, const double* d_sumsq_total, long ncells_total, void* cuda_stream)
+{
+    int rc = check_dims(nx, ny, nz, bx, by, bz);
+    if (rc) return rc;
+    if (!d_stream || (!use_local_rms && !d_sumsq_total)) return fail(CVXGPU_ERR_ARG, "cvxgpu_write_header_device: null pointer");
+    Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    CU(launch_write_header(d_stream, s, scale, use_local_rms ? 1 : 0, d_sumsq_total, ncells_total, nullptr, (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_offsets_add_device(unsigned long long* d_offs, long n, long base, void* cuda_stream)
+{
+    if (!d_offs || n < 0 || base < 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_offsets_add_device: bad argument");
+    CU(launch_offsets_add(d_offs, n, base, (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_encode_blocks_device(cvxgpu_workspace* wsin, const float* d_vol, int nx, int ny, int nz_slab,
+                                           int bx, int by, int bz, float scale, int use_local_rms,
+                                           const double* d_sumsq_total, long ncells_total,
+                                           unsigned long long* d_offs, float* d_blkmulfac,
+                                           void* d_payload, long payload_capacity,
+                                           long* d_payload_bytes, int* d_status, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    rc = check_dims(nx, ny, nz_slab, bx, by, bz);
+    if (rc) return rc;
+    const int local = use_local_rms ? 1 : 0;
+    if (!d_vol || !d_offs || !d_payload || !d_payload_bytes || !d_status || (local && !d_blkmulfac) || (!local && !d_sumsq_total))
+        return fail(CVXGPU_ERR_ARG, "cvxgpu_encode_blocks_device: null pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    Shape s = make_shape(nx, ny, nz_slab, bx, by, bz);
+    CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
+    CU(launch_write_header(nullptr, s, scale, local, d_sumsq_total, ncells_total, ws->d_mulfac, st));
+    CU(launch_encode(ws, d_vol, s, scale, local, ws->d_mulfac, d_offs, d_blkmulfac, d_payload, payload_capacity,
+                     d_payload_bytes, d_status, exact_mode(), st));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_decode_blocks_device(cvxgpu_workspace* wsin, float* d_vol_slab, int nx, int ny, int nz_slab,
+                                           int bx, int by, int bz, float glob_mulfac, int use_local_rms,
+                                           const unsigned long long* d_offs, const float* d_blkmulfac,
+                                           const void* d_payload, long payload_bytes, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    rc = check_dims(nx, ny, nz_slab, bx, by, bz);
+    if (rc) return rc;
+    const int local = use_local_rms ? 1 : 0;
+    if (!d_vol_slab || !d_offs || !d_payload || (local && !d_blkmulfac) || payload_bytes < 0)
+        return fail(CVXGPU_ERR_ARG, "cvxgpu_decode_blocks_device: bad argument");
+    Shape s = make_shape(nx, ny, nz_slab, bx, by, bz);
+    CU(launch_decode(ws, d_vol_slab, s, glob_mulfac, local, d_offs, d_blkmulfac, d_payload, payload_bytes, exact_mode(),
+                     (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_wavelet_blocks_device(cvxgpu_workspace* wsin, float* d_blocks, long nblocks, int bx, int by, int bz,
+                                            int inverse, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    if (!valid_block_size(bx, by, bz)) return fail(CVXGPU_ERR_ARG, "invalid block size %d x %d x %d", bx, by, bz);
+    if (!d_blocks || nblocks < 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_wavelet_blocks_device: bad argument");
+    CU(launch_wavelet(ws, d_blocks, nblocks, bx, by, bz, inverse ? 1 : 0, exact_mode(), (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+// ---- whole-volume calls ---------------------------------------------------------------------
+static int compress_enqueue(cvxgpu_workspace* ws, const float* d_vol, const Shape& s, float scale, int local,
+                            void* d_stream, long capacity, long* d_length, int* d_status, cudaStream_t st)
+{
+    const long tables = 8 * s.nblk + (local ? 4 * s.nblk : 0);
+    if (capacity < 32 + tables + 7) return fail(CVXGPU_ERR_CAPACITY, "capacity %ld is smaller than header + tables (%ld bytes)", capacity, 32 + tables + 7);
+    if (reinterpret_cast<uintptr_t>(d_stream) & 7) return fail(CVXGPU_ERR_ARG, "compressed stream must be 8-byte aligned");
+    unsigned char* base = reinterpret_cast<unsigned char*>(d_stream);
+    unsigned long long* d_offs = reinterpret_cast<unsigned long long*>(base + 32);          // CvxCompress.cpp:302
+    float* d_bmf = local ? reinterpret_cast<float*>(base + 32 + 8 * s.nblk) : nullptr;     // :308
+    unsigned char* d_payload = base + 32 + tables;                                          // :309 / :314
+    const long ncells = (long)s.nx * s.ny * s.nz;
+    CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
+    if (!local) CU(launch_sumsq(ws, d_vol, ncells, ws->d_sumsq, st));
+    CU(launch_write_header(d_stream, s, scale, local, ws->d_sumsq, ncells, ws->d_mulfac, st));
+    CU(launch_encode(ws, d_vol, s, scale, local, ws->d_mulfac, d_offs, d_bmf, d_payload, capacity - 32 - tables - 7,
+                     ws->d_payload_bytes, d_status, exact_mode(), st));
+    CU(launch_finish_length(ws->d_payload_bytes, tables, d_length, st));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_compress_device_async(cvxgpu_workspace* wsin, const float* d_vol, int nx, int ny, int nz,
+                                            int bx, int by, int bz, float scale, int use_local_rms,
+                                            void* d_stream, long capacity, long* d_length, int* d_status, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    rc = check_dims(nx, ny, nz, bx, by, bz);
+    if (rc) return rc;
+    if (!d_vol || !d_stream || !d_length || !d_status) return fail(CVXGPU_ERR_ARG, "cvxgpu_compress_device_async: null pointer");
+    Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    return compress_enqueue(ws, d_vol, s, scale, use_local_rms ? 1 : 0, d_stream, capacity, d_length, d_status, (cudaStream_t)cuda_stream);
+}
+
+extern "C" int cvxgpu_compress_device(cvxgpu_workspace* wsin, const float* d_vol, int nx, int ny, int nz,
+                                      int bx, int by, int bz, float scale, int use_local_rms,
+                                      void* d_stream, long capacity, long* length, float* ratio, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    rc = check_dims(nx, ny, nz, bx, by, bz);
+    if (rc) return rc;
+    if (!d_vol || !d_stream || !length) return fail(CVXGPU_ERR_ARG, "cvxgpu_compress_device: null pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    rc = compress_enqueue(ws, d_vol, s, scale, use_local_rms ? 1 : 0, d_stream, capacity, ws->d_length, ws->d_err, st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(ws->h_pinned, ws->d_length, 16, cudaMemcpyDeviceToHost, st));       // length (8) + err (4 of the next 8)
+    CU(cudaStreamSynchronize(st));
+    long len;
+    int err;
+    memcpy(&len, ws->h_pinned, 8);
+    memcpy(&err, ws->h_pinned + 8, 4);
+    *length = len;
+    if (ratio) *ratio = (float)(((double)nx * (double)ny * (double)nz * 4.0) / (double)len);      // CvxCompress.cpp:425
+    if (err != 0) return fail(CVXGPU_ERR_CAPACITY, "compressed stream needs %ld bytes but capacity is %ld", len, capacity);
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_parse_header(const void* h_stream, long length, int* nx, int* ny, int* nz,
+                                   int* bx, int* by, int* bz, float* glob_mulfac, int* flags)
+{
+    if (!h_stream || length < 32) return fail(CVXGPU_ERR_STREAM, "stream shorter than its 32-byte header");
+    int32_t h[8];
+    memcpy(h, h_stream, 32);
+    if (h[0] <= 0 || h[1] <= 0 || h[2] <= 0 || !valid_block_size(h[3], h[4], h[5]))
+        return fail(CVXGPU_ERR_STREAM, "bad header: volume %d x %d x %d, block %d x %d x %d", h[0], h[1], h[2], h[3], h[4], h[5]);
+    if (nx) *nx = h[0];
+    if (ny) *ny = h[1];
+    if (nz) *nz = h[2];
+    if (bx) *bx = h[3];
+    if (by) *by = h[4];
+    if (bz) *bz = h[5];
+    if (glob_mulfac) memcpy(glob_mulfac, &h[6], 4);
+    if (flags) *flags = h[7];
+    return CVXGPU_OK;
+}
+
+static int decompress_with_header(cvxgpu_workspace* ws, float* d_vol, int nx, int ny, int nz, const int32_t* h,
+                                  const void* d_stream, long length, cudaStream_t st)
+{
+    int hx, hy, hz, bx, by, bz, flags;
+    float gm;
+    int rc = cvxgpu_parse_header(h, 32, &hx, &hy, &hz, &bx, &by, &bz, &gm, &flags);
+    if (rc) return rc;
+    if (hx != nx || hy != ny || hz != nz)        // CvxCompress.cpp:473-488 prints and asserts
+        return fail(CVXGPU_ERR_STREAM, "stream holds a %d x %d x %d volume, caller expects %d x %d x %d", hx, hy, hz, nx, ny, nz);
+    const int local = flags & 1;
+    Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    const long tables = 8 * s.nblk + (local ? 4 * s.nblk : 0);
+    // `length` is informative in the reference (never read); here it bounds the reads when given
+    long payload_bytes = length > 0 ? length - 32 - tables : (1L << 62);
+    if (payload_bytes < 0) return fail(CVXGPU_ERR_STREAM, "stream length %ld is shorter than header + tables", length);
+    const unsigned char* base = reinterpret_cast<const unsigned char*>(d_stream);
+    const unsigned long long* d_offs = reinterpret_cast<const unsigned long long*>(base + 32);
+    const float* d_bmf = local ? reinterpret_cast<const float*>(base + 32 + 8 * s.nblk) : nullptr;
+    CU(launch_decode(ws, d_vol, s, gm, local, d_offs, d_bmf, base + 32 + tables, payload_bytes, exact_mode(), st));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_decompress_device(cvxgpu_workspace* wsin, float* d_vol, int nx, int ny, int nz,
+                                        const void* d_stream, long length, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws);
+    if (rc) return rc;
+    if (!d_vol || !d_stream) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress_device: null pointer");
+    if (reinterpret_cast<uintptr_t>(d_stream) & 7) return fail(CVXGPU_ERR_ARG, "compressed stream must be 8-byte aligned");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    CU(cudaMemcpyAsync(ws->h_pinned + 64, d_stream, 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    int32_t h[8];
+    memcpy(h, ws->h_pinned + 64, 32);
+    return decompress_with_header(ws, d_vol, nx, ny, nz, h, d_stream, length, st);
+}
+
+// ---- host-pointer entry points ----------------------------------------------------------------
+// 0: host (pageable or pinned), 1: device-accessible (device or managed)
+static int pointer_on_device(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? 1 : 0;
+}
+
+static int reserve(unsigned char** p, size_t* have, size_t want)
+{
+    if (want <= *have) return CVXGPU_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    CU(cudaMalloc(p, want));
+    *have = want;
+    return CVXGPU_OK;
+}
+
+// chunked copies keep pageable transfers pipelined inside the driver and bound pinned staging
+static int copy_chunked(void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st)
+{
+    const size_t chunk = 256ull << 20;
+    for (size_t o = 0; o < bytes; o += chunk) {
+        size_t n = bytes - o < chunk ? bytes - o : chunk;
+        CU(cudaMemcpyAsync(static_cast<unsigned char*>(dst) + o, static_cast<const unsigned char*>(src) + o, n, kind, st));
+    }
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx, int by, int bz, float scale,
+                               int use_local_rms, void* stream_out, long* length, float* ratio)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(nullptr, &ws);
+    if (rc) return rc;
+    rc = check_dims(nx, ny, nz, bx, by, bz);
+    if (rc) return rc;
+    if (!vol || !stream_out || !length) return fail(CVXGPU_ERR_ARG, "cvxgpu_compress: null pointer");
+    const int local = use_local_rms ? 1 : 0;
+    const size_t vol_bytes = (size_t)nx * ny * nz * 4;
+    const long max_bytes = cvxgpu_max_compressed_bytes(nx, ny, nz, bx, by, bz, local);
+    const int vol_dev = pointer_on_device(vol), out_dev = pointer_on_device(stream_out);
+    cudaStream_t st = 0;
+    const float* d_vol = vol;
+    if (!vol_dev) {
+        rc = reserve(&ws->d_stage_vol, &ws->stage_vol_bytes, vol_bytes);
+        if (rc) return rc;
+        rc = copy_chunked(ws->d_stage_vol, vol, vol_bytes, cudaMemcpyHostToDevice, st);
+        if (rc) return rc;
+        d_vol = reinterpret_cast<const float*>(ws->d_stage_vol);
+    }
+    if (out_dev) {
+        // the class API has no capacity argument (CvxCompress.hxx:32-45): the caller's buffer is trusted
+        return cvxgpu_compress_device(ws, d_vol, nx, ny, nz, bx, by, bz, scale, local, stream_out, max_bytes, length, ratio, st);
+    }
+    // first try a stream of at most a quarter of the volume (+ tables); if a block mix needs more, retry with the worst case
+    const Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    long cap = 32 + 8 * s.nblk + (local ? 4 * s.nblk : 0) + (long)(vol_bytes / 4) + 4096;
+    if (cap > max_bytes) cap = max_bytes;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        rc = reserve(&ws->d_stage_stream, &ws->stage_stream_bytes, (size_t)cap + 64);
+        if (rc) return rc;
+        rc = cvxgpu_compress_device(ws, d_vol, nx, ny, nz, bx, by, bz, scale, local, ws->d_stage_stream, cap, length, ratio, st);
+        if (rc != CVXGPU_ERR_CAPACITY || cap == max_bytes) break;
+        cap = max_bytes;
+    }
+    if (rc) return rc;
+    // only [0, length - 7) is written: the final 7 slack bytes are never touched (CvxCompress.cpp:421)
+    rc = copy_chunked(stream_out, ws->d_stage_stream, (size_t)(*length - 7), cudaMemcpyDeviceToHost, st);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(st));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void* stream_in, long length)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(nullptr, &ws);
+    if (rc) return rc;
+    if (!vol || !stream_in) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: null pointer");
+    const int vol_dev = pointer_on_device(vol), in_dev = pointer_on_device(stream_in);
+    cudaStream_t st = 0;
+    if (in_dev && vol_dev) return cvxgpu_decompress_device(ws, vol, nx, ny, nz, stream_in, length, st);
+    int32_t h[8];
+    if (in_dev) {
+        CU(cudaMemcpy(h, stream_in, 32, cudaMemcpyDeviceToHost));
+    } else {
+        memcpy(h, stream_in, 32);
+    }
+    int hx, hy, hz, bx, by, bz, flags;
+    rc = cvxgpu_parse_header(h, 32, &hx, &hy, &hz, &bx, &by, &bz, nullptr, &flags);
+    if (rc) return rc;
+    const void* d_stream = stream_in;
+    if (!in_dev) {
+        // the reference never reads compressed_length (CvxCompress.cpp:463-571); callers may pass 0
+        long len = length;
+        if (len <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: compressed_length is required for host streams");
+        rc = reserve(&ws->d_stage_stream, &ws->stage_stream_bytes, (size_t)len + 64);
+        if (rc) return rc;
+        rc = copy_chunked(ws->d_stage_stream, stream_in, (size_t)(len - 7 > 32 ? len - 7 : len), cudaMemcpyHostToDevice, st);
+        if (rc) return rc;
+        d_stream = ws->d_stage_stream;
+    }
+    const size_t vol_bytes = (size_t)nx * ny * nz * 4;
+    float* d_vol = vol;
+    if (!vol_dev) {
+        rc = reserve(&ws->d_stage_vol, &ws->stage_vol_bytes, vol_bytes);
+        if (rc) return rc;
+        d_vol = reinterpret_cast<float*>(ws->d_stage_vol);
+    }
+    rc = decompress_with_header(ws, d_vol, nx, ny, nz, h, d_stream, length, st);
+    if (rc) return rc;
+    if (!vol_dev) {
+        rc = copy_chunked(vol, d_vol, vol_bytes, cudaMemcpyDeviceToHost, st);
+        if (rc) return rc;
+    }
+    CU(cudaStreamSynchronize(st));
+    return CVXGPU_OK;
+}
+
+// 32 header bytes of a stream that may live in host or device memory (used by the class's
+// out-of-place Decompress, which must size its result before decoding)
+int cvx_internal_fetch_header(const void* stream, unsigned char* hdr)
+{
+    if (!stream) return fail(CVXGPU_ERR_ARG, "null stream");
+    if (pointer_on_device(stream)) {
+        CU(cudaMemcpy(hdr, stream, 32, cudaMemcpyDeviceToHost));
+    } else {
+        memcpy(hdr, stream, 32);
+    }
+    return CVXGPU_OK;
+}

@@ -1,0 +1,909 @@
+// cvx_kernels.cu -- sm_100a kernels of the CvxCompress hot path and their launchers.
+//
+//   k_sumsq / k_rms_finish   Compute_Global_RMS              CvxCompress.cpp:73-117
+//   k_encode_fused           Copy_To_Block + Wavelet_Transform_Fast_Forward + Compute_Local_RMS +
+//                            Run_Length_Encode_Slow + raw fallback + offset table
+//                            (CvxCompress.cpp:318-420), one CTA per block, block in shared memory
+//   k_decode_fused           Run_Length_Decode_Slow + Wavelet_Transform_Fast_Inverse + Copy_From_Block
+//                            (CvxCompress.cpp:528-568)
+//   k_wavelet_fused          forward or inverse transform of dense blocks (module-test sweep)
+//   k_stage_*                the same pipeline staged through global scratch for block shapes
+//                            that do not fit shared memory (any dimension > 64 or > 32768 cells)
+//
+// Data layout in HBM: the volume is nx-fastest fp32; the stream is the reference's byte
+// format.  A block lives in shared memory as a dense, XOR-swizzled array (cvx_device.cuh).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "cvx_wavelet.cuh"
+#include "cvx_rle.cuh"
+#include "cvx_device.cuh"
+#include "cvx_codec.cuh"
+#include "cvx_internal.h"
+
+namespace cvx {
+
+// ------------------------------------------------------------------------------------------
+// Global RMS: per-CTA fp64 partial sums of v*v, then a fixed-order final sum (deterministic).
+// ------------------------------------------------------------------------------------------
+constexpr int SUMSQ_T = 256;
+
+__global__ void __launch_bounds__(SUMSQ_T) k_sumsq(const float* __restrict__ vol, long n, double* __restrict__ partial)
+{
+    const long nthreads = (long)gridDim.x * SUMSQ_T;
+    const long gtid = (long)blockIdx.x * SUMSQ_T + threadIdx.x;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    // peel to 16-byte alignment, then float4
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(vol);
+    long head = ((16 - (addr & 15)) & 15) >> 2;
+    if (head > n) head = n;
+    if (gtid < head) { double d = vol[gtid]; a0 += d * d; }
+    const float4* v4 = reinterpret_cast<const float4*>(vol + head);
+    const long n4 = (n - head) >> 2;
+    for (long i = gtid; i < n4; i += nthreads) {
+        float4 q = __ldg(&v4[i]);
+        double d0 = q.x, d1 = q.y, d2 = q.z, d3 = q.w;
+        a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
+    }
+    const long tail0 = head + (n4 << 2);
+    if (gtid < n - tail0) { double d = vol[tail0 + gtid]; a1 += d * d; }
+    double s = (a0 + a1) + (a2 + a3);
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    __shared__ double sw[SUMSQ_T / 32];
+    if (lane_id() == 0) sw[warp_id()] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < SUMSQ_T / 32; ++w) t += sw[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+__global__ void k_sumsq_finish(const double* __restrict__ partial, int n, double* __restrict__ out)
+{
+    // one warp, fixed order: lane-strided partial sums, then a shuffle tree
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += 32) s += partial[i];
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if (threadIdx.x == 0) *out = s;
+}
+
+// glob_mulfac = 1 / (rms * scale), 1 when rms == 0 or the result is not finite (CvxCompress.cpp:291-295);
+// rms = (float)sqrt(sumsq / N) (:115-116).  With local RMS the global rms is taken as 1 (:249).
+__device__ __forceinline__ float glob_mulfac_of(const double* sumsq, long ncells, float scale, int use_local)
+{
+    float rms = 1.0f;
+    if (!use_local) rms = (float)sqrt(*sumsq / (double)ncells);
+    float m = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, scale)) : 1.0f;
+    if (!isfinite(m)) m = 1.0f;
+    return m;
+}
+
+__global__ void k_write_header(int32_t* hdr, int nx, int ny, int nz, int bx, int by, int bz, float scale, int use_local,
+                               const double* sumsq, long ncells, float* mulfac_out)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        float m = glob_mulfac_of(sumsq, ncells, scale, use_local);
+        if (hdr) {
+            hdr[0] = nx; hdr[1] = ny; hdr[2] = nz; hdr[3] = bx; hdr[4] = by; hdr[5] = bz;
+            hdr[6] = __float_as_int(m);
+            hdr[7] = use_local ? 1 : 0;
+        }
+        if (mulfac_out) *mulfac_out = m;
+    }
+}
+
+__global__ void k_offsets_add(unsigned long long* offs, long n, unsigned long long base)
+{
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) offs[i] += base;          // bit 63 (raw flag) is untouched: base < 2^63
+}
+
+// length = 32 + 8*nnn [+ 4*nnn] + payload + 7  (CvxCompress.cpp:421-422)
+__global__ void k_finish_length(const long* payload_bytes, long table_bytes, long* length)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) *length = 32 + table_bytes + *payload_bytes + 7;
+}
+
+// ------------------------------------------------------------------------------------------
+// Transform passes on a block in shared memory.  One thread owns one line, in registers.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int physr(int i, int sh) { return i ^ (((i >> sh) & 7) << 2); }
+
+// x lines: the thread's row is contiguous -> LDS.128 / STS.128, conflict-free by the swizzle
+template <int N, bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void pass_x(float* sm, int nrows)
+{
+    constexpr int SH = Swz<N>::SH;
+    for (int r = threadIdx.x; r < nrows; r += T) {
+        const int base = r * N;
+        float in[N], v[N];
+#pragma unroll
+        for (int c = 0; c < N / 4; ++c) {
+            float4 q = *reinterpret_cast<const float4*>(&sm[physr(base + 4 * c, SH)]);
+            in[4 * c] = q.x; in[4 * c + 1] = q.y; in[4 * c + 2] = q.z; in[4 * c + 3] = q.w;
+        }
+        if (FWD) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) v[i] = in[i];
+            fwd_line<N, EXACT>(v);
+#pragma unroll
+            for (int c = 0; c < N / 4; ++c) {
+                float4 q;
+                q.x = v[sub_to_reg<N, EXACT>(4 * c)]; q.y = v[sub_to_reg<N, EXACT>(4 * c + 1)];
+                q.z = v[sub_to_reg<N, EXACT>(4 * c + 2)]; q.w = v[sub_to_reg<N, EXACT>(4 * c + 3)];
+                *reinterpret_cast<float4*>(&sm[physr(base + 4 * c, SH)]) = q;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; ++i) v[sub_to_reg<N, EXACT>(i)] = in[i];
+            inv_line<N, EXACT>(v);
+#pragma unroll
+            for (int c = 0; c < N / 4; ++c) {
+                float4 q = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+                *reinterpret_cast<float4*>(&sm[physr(base + 4 * c, SH)]) = q;
+            }
+        }
+    }
+}
+
+// strided lines (y: stride BX, z: stride BX*BY): consecutive lanes own consecutive x
+template <int N, bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void pass_strided(float* sm, int nlines, int lbx, int group_stride, int stride, int sh)
+{
+    // line l: x = l & (BX-1), g = l >> lbx; first element at g * group_stride + x
+    for (int l = threadIdx.x; l < nlines; l += T) {
+        const int base = (l >> lbx) * group_stride + (l & ((1 << lbx) - 1));
+        float v[N];
+        if (FWD) {
+#pragma unroll
+            for (int j = 0; j < N; ++j) v[j] = sm[physr(base + j * stride, sh)];
+            fwd_line<N, EXACT>(v);
+#pragma unroll
+            for (int r = 0; r < N; ++r) sm[physr(base + reg_to_sub<N, EXACT>(r) * stride, sh)] = v[r];
+        } else {
+#pragma unroll
+            for (int r = 0; r < N; ++r) v[r] = sm[physr(base + reg_to_sub<N, EXACT>(r) * stride, sh)];
+            inv_line<N, EXACT>(v);
+#pragma unroll
+            for (int j = 0; j < N; ++j) sm[physr(base + j * stride, sh)] = v[j];
+        }
+    }
+}
+
+template <int MAXN, bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void pass_x_n(float* sm, int n, int nrows)
+{
+    switch (n) {
+    case 8: pass_x<8, EXACT, FWD, T>(sm, nrows); break;
+    case 16: pass_x<16, EXACT, FWD, T>(sm, nrows); break;
+    case 32: pass_x<32, EXACT, FWD, T>(sm, nrows); break;
+    case 64: if constexpr (MAXN >= 64) pass_x<64, EXACT, FWD, T>(sm, nrows); break;
+    default: break;
+    }
+}
+template <int MAXN, bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void pass_strided_n(float* sm, int n, int nlines, int lbx, int group_stride, int stride, int sh)
+{
+    switch (n) {
+    case 8: pass_strided<8, EXACT, FWD, T>(sm, nlines, lbx, group_stride, stride, sh); break;
+    case 16: pass_strided<16, EXACT, FWD, T>(sm, nlines, lbx, group_stride, stride, sh); break;
+    case 32: pass_strided<32, EXACT, FWD, T>(sm, nlines, lbx, group_stride, stride, sh); break;
+    case 64: if constexpr (MAXN >= 64) pass_strided<64, EXACT, FWD, T>(sm, nlines, lbx, group_stride, stride, sh); break;
+    default: break;
+    }
+}
+
+struct BlkShape {
+    int bx, by, bz;       // block dims (bz may be 1)
+    int lbx, lby;         // log2
+    int B;                // cells
+    int sh;               // swizzle shift
+};
+
+// forward: x, y (per z-slice) then z (Wavelet_Transform_Fast.cpp:24-145); inverse: same axis order
+// with the synthesis operator (:148-279)
+template <int MAXN, bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void transform_block(float* sm, const BlkShape& s)
+{
+    pass_x_n<MAXN, EXACT, FWD, T>(sm, s.bx, s.by * s.bz);
+    __syncthreads();
+    pass_strided_n<MAXN, EXACT, FWD, T>(sm, s.by, s.bx * s.bz, s.lbx, s.bx * s.by, s.bx, s.sh);
+    __syncthreads();
+    if (s.bz > 1) {
+        pass_strided_n<MAXN, EXACT, FWD, T>(sm, s.bz, s.bx * s.by, s.lbx + s.lby, 0, s.bx * s.by, s.sh);
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Copy_To_Block / Copy_From_Block (Block_Copy.cpp:21-116, :136-212) between the volume and the
+// swizzled shared-memory block.  vec_ok: nx % 4 == 0 and the volume base is 16-byte aligned, so
+// every block row starts on a 16-byte boundary and 128-bit accesses are legal.
+// ------------------------------------------------------------------------------------------
+struct VolView {
+    int nx, ny, nz;
+    int vec_ok;
+};
+
+template <int T>
+__device__ __forceinline__ void gather_block(float* sm, const float* __restrict__ vol, const VolView& g,
+                                             int x0, int y0, int z0, const BlkShape& s)
+{
+    if (g.vec_ok) {
+        const int lcpr = s.lbx - 2;
+        const int nchunks = s.B >> 2;
+#pragma unroll 4
+        for (int idx = threadIdx.x; idx < nchunks; idx += T) {
+            const int c = idx & ((1 << lcpr) - 1);
+            const int r = idx >> lcpr;
+            const int gy = y0 + (r & (s.by - 1)), gz = z0 + (r >> s.lby), gx = x0 + 4 * c;
+            float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gy < g.ny && gz < g.nz && gx < g.nx)
+                q = __ldg(reinterpret_cast<const float4*>(vol + ((long)gz * g.ny + gy) * g.nx + gx));
+            *reinterpret_cast<float4*>(&sm[physr(4 * idx, s.sh)]) = q;
+        }
+    } else {
+#pragma unroll 4
+        for (int i = threadIdx.x; i < s.B; i += T) {
+            const int x = i & (s.bx - 1);
+            const int r = i >> s.lbx;
+            const int gy = y0 + (r & (s.by - 1)), gz = z0 + (r >> s.lby), gx = x0 + x;
+            float q = 0.f;
+            if (gy < g.ny && gz < g.nz && gx < g.nx) q = __ldg(vol + ((long)gz * g.ny + gy) * g.nx + gx);
+            sm[physr(i, s.sh)] = q;
+        }
+    }
+}
+
+template <int T>
+__device__ __forceinline__ void scatter_block(const float* sm, float* __restrict__ vol, const VolView& g,
+                                              int x0, int y0, int z0, const BlkShape& s)
+{
+    if (g.vec_ok) {
+        const int lcpr = s.lbx - 2;
+        const int nchunks = s.B >> 2;
+#pragma unroll 4
+        for (int idx = threadIdx.x; idx < nchunks; idx += T) {
+            const int c = idx & ((1 << lcpr) - 1);
+            const int r = idx >> lcpr;
+            const int gy = y0 + (r & (s.by - 1)), gz = z0 + (r >> s.lby), gx = x0 + 4 * c;
+            if (gy < g.ny && gz < g.nz && gx < g.nx) {
+                float4 q = *reinterpret_cast<const float4*>(&sm[physr(4 * idx, s.sh)]);
+                *reinterpret_cast<float4*>(vol + ((long)gz * g.ny + gy) * g.nx + gx) = q;
+            }
+        }
+    } else {
+#pragma unroll 4
+        for (int i = threadIdx.x; i < s.B; i += T) {
+            const int x = i & (s.bx - 1);
+            const int r = i >> s.lbx;
+            const int gy = y0 + (r & (s.by - 1)), gz = z0 + (r >> s.lby), gx = x0 + x;
+            if (gy < g.ny && gz < g.nz && gx < g.nx) vol[((long)gz * g.ny + gy) * g.nx + gx] = sm[physr(i, s.sh)];
+        }
+    }
+}
+
+// sum of squares of the block's coefficients over the CTA (Compute_Local_RMS, CvxCompress.cpp:119-142;
+// the summation order differs from the reference's 8 serial lanes, so blkmulfac may differ in the
+// last bits -- the value travels in the stream, so decoding is unaffected)
+template <int T>
+__device__ __forceinline__ float cta_sumsq(const float* sm, int B, float* s_red)
+{
+    float a = 0.f;
+    for (int i = threadIdx.x; i < (B >> 2); i += T) {
+        float4 q = reinterpret_cast<const float4*>(sm)[i];     // any order: the swizzle is a permutation
+        a = __fmaf_rn(q.x, q.x, a); a = __fmaf_rn(q.y, q.y, a); a = __fmaf_rn(q.z, q.z, a); a = __fmaf_rn(q.w, q.w, a);
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+    if (lane_id() == 0) s_red[warp_id()] = a;
+    __syncthreads();
+    float t = 0.f;
+    for (int w = 0; w < (T + 31) / 32; ++w) t += s_red[w];
+    __syncthreads();
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused encode: persistent CTAs take blocks in natural order from an atomic ticket.
+// ------------------------------------------------------------------------------------------
+struct EncParams {
+    const float* vol;
+    VolView g;
+    BlkShape s;
+    int nbx, nby;
+    long nblk;
+    float scale;
+    int use_local;
+    const float* glob_mulfac;        // device scalar
+    unsigned long long* offs;        // nblk
+    float* blkmulfac;                // nblk or null
+    uint8_t* payload;
+    long cap;
+    unsigned long long* status;      // nblk look-back words, zeroed
+    unsigned int* ticket;            // zeroed
+    long* payload_bytes;             // out
+    int* err;                        // out: set to CVXGPU_ERR_CAPACITY on overflow
+    int nseg, gps;                   // RLE segmentation of a block
+};
+
+constexpr int SEG_CAP = 1024;
+
+// raw fallback payload: B fp32 coefficients in raster order (CvxCompress.cpp:355-360)
+template <int T, class Phys>
+__device__ __forceinline__ void store_raw(const float* coef, long B, uint8_t* dst, Phys phys)
+{
+    if ((reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+        float* d = reinterpret_cast<float*>(dst);
+        for (long i = threadIdx.x; i < B; i += T) d[i] = coef[phys(i)];
+    } else {
+        for (long i = threadIdx.x; i < B; i += T) {
+            uint32_t u = __float_as_uint(coef[phys(i)]);
+            dst[4 * i] = (uint8_t)u; dst[4 * i + 1] = (uint8_t)(u >> 8);
+            dst[4 * i + 2] = (uint8_t)(u >> 16); dst[4 * i + 3] = (uint8_t)(u >> 24);
+        }
+    }
+}
+
+// shared tail of the fused and the staged encoders: plan, look-back, table entry, emit
+template <int T, class Get8, class Phys>
+__device__ __forceinline__ void encode_tail(const EncParams& p, long t, const float* coef, float mulfac,
+                                            Get8 get8, Phys phys, int4* s_seg, int* scratch, unsigned long long* s_off)
+{
+    const long B = p.s.B;
+    int len = cta_rle_plan<T>(p.nseg, p.gps, mulfac, get8, s_seg, scratch);
+    const bool raw = (long)len > 4 * B;                   // CvxCompress.cpp:350
+    const unsigned long long nbytes = raw ? (unsigned long long)(4 * B) : (unsigned long long)len;
+    if (warp_id() == 0) {
+        unsigned long long excl = lookback_exclusive(p.status, t, nbytes);
+        if (lane_id() == 0) {
+            *s_off = excl;
+            p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);      // :382-384
+            if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + nbytes);
+        }
+    }
+    __syncthreads();
+    const unsigned long long off = *s_off;
+    if ((long)(off + nbytes) > p.cap) {
+        if (threadIdx.x == 0) *p.err = -3;
+    } else {
+        uint8_t* dst = p.payload + off;
+        if (raw) store_raw<T>(coef, B, dst, phys);
+        else cta_rle_emit<T>(p.nseg, p.gps, mulfac, get8, s_seg, [&](int pos, uint8_t b) { dst[pos] = b; });
+    }
+    __syncthreads();
+}
+
+template <int MAXN, bool EXACT, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB) k_encode_fused(const EncParams p)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    int4* s_seg = reinterpret_cast<int4*>(smem_raw + (size_t)p.s.B * 4);
+    __shared__ int scratch[72];
+    __shared__ float s_red[32];
+    __shared__ unsigned int s_ticket;
+    __shared__ unsigned long long s_off;
+    const BlkShape s = p.s;
+    const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
+    for (;;) {
+        if (threadIdx.x == 0) s_ticket = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+        const long t = s_ticket;
+        if (t >= p.nblk) break;
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        gather_block<T>(sm, p.vol, p.g, iix * s.bx, iiy * s.by, iiz * s.bz, s);
+        __syncthreads();
+        transform_block<MAXN, EXACT, true, T>(sm, s);
+        float mulfac = gmul;
+        if (p.use_local) {
+            float ss = cta_sumsq<T>(sm, s.B, s_red);
+            float rms = sqrtf(__fdiv_rn(ss, (float)s.B));
+            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;     // CvxCompress.cpp:346
+            if (threadIdx.x == 0) p.blkmulfac[t] = mulfac;
+        }
+        const int sh = s.sh;
+        auto get8 = [&](int g, float* c) {
+            const int i = g * 8;
+            float4 a = *reinterpret_cast<const float4*>(&sm[physr(i, sh)]);
+            float4 b = *reinterpret_cast<const float4*>(&sm[physr(i + 4, sh)]);
+            c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+        };
+        encode_tail<T>(p, t, sm, mulfac, get8, [sh](long i) { return (long)physr((int)i, sh); }, s_seg, scratch, &s_off);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused decode
+// ------------------------------------------------------------------------------------------
+struct DecParams {
+    float* vol;
+    VolView g;
+    BlkShape s;
+    int nbx, nby;
+    long nblk;
+    float glob_mulfac;
+    int use_local;
+    const unsigned long long* offs;
+    const float* blkmulfac;
+    const uint8_t* payload;
+    long payload_bytes;
+};
+
+template <int T, class PutV, class Phys>
+__device__ __forceinline__ void decode_head(const DecParams& p, long t, float* coef, PutV put, Phys phys,
+                                            uint32_t* s_win, int* s_ext, int* scratch)
+{
+    const long B = p.s.B;
+    unsigned long long o = p.offs[t];
+    const bool raw = (o >> 63) != 0;                               // CvxCompress.cpp:545-547
+    o &= 0x7FFFFFFFFFFFFFFFull;
+    const uint8_t* lo = p.payload;
+    const uint8_t* hi = p.payload + p.payload_bytes;
+    const uint8_t* src = p.payload + o;
+    if (raw) {                                                     // :555
+        if ((reinterpret_cast<uintptr_t>(src) & 3) == 0 && src + 4 * B <= hi) {
+            const float* f = reinterpret_cast<const float*>(src);
+            for (long i = threadIdx.x; i < B; i += T) coef[phys(i)] = f[i];
+        } else {
+            for (long i = threadIdx.x; i < B; i += T) {
+                uint32_t u = 0;
+                for (int k = 0; k < 4; ++k) {
+                    const uint8_t* b = src + 4 * i + k;
+                    if (b < hi) u |= (uint32_t)(*b) << (8 * k);
+                }
+                coef[phys(i)] = __uint_as_float(u);
+            }
+        }
+    } else {
+        float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
+        float scalefac = __fdiv_rn(1.0f, mulfac);                  // Run_Length_Encode_Slow.cpp:392
+        cta_rle_decode<T>(lo, hi, src, (int)B, scalefac, put, s_win, s_ext, scratch);
+    }
+    __syncthreads();
+}
+
+template <int MAXN, bool EXACT, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams p)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    uint32_t* s_win = reinterpret_cast<uint32_t*>(smem_raw + (size_t)p.s.B * 4);
+    int* s_ext = reinterpret_cast<int*>(s_win + (T + 2) * 4);
+    __shared__ int scratch[72];
+    const BlkShape s = p.s;
+    const int sh = s.sh;
+    for (long t = blockIdx.x; t < p.nblk; t += gridDim.x) {
+        for (int i = threadIdx.x; i < (s.B >> 2); i += T) reinterpret_cast<float4*>(sm)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        decode_head<T>(p, t, sm, [&](int i, float v) { sm[physr(i, sh)] = v; },
+                       [sh](long i) { return (long)physr((int)i, sh); }, s_win, s_ext, scratch);
+        transform_block<MAXN, EXACT, false, T>(sm, s);
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        scatter_block<T>(sm, p.vol, p.g, iix * s.bx, iiy * s.by, iiz * s.bz, s);
+        __syncthreads();
+    }
+}
+
+// forward / inverse transform of dense blocks: block k is the z-range [k*bz, (k+1)*bz) of a
+// bx * by * (bz*nblocks) volume
+template <int MAXN, bool EXACT, bool FWD, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB) k_wavelet_fused(float* blocks, long nblocks, const BlkShape s)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    VolView g; g.nx = s.bx; g.ny = s.by; g.nz = s.bz; g.vec_ok = 1;
+    for (long k = blockIdx.x; k < nblocks; k += gridDim.x) {
+        float* blk = blocks + k * (long)s.B;
+        gather_block<T>(sm, blk, g, 0, 0, 0, s);
+        __syncthreads();
+        transform_block<MAXN, EXACT, FWD, T>(sm, s);
+        scatter_block<T>(sm, blk, g, 0, 0, 0, s);
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Staged path (any valid block shape): blocks of a batch are dense arrays in global scratch.
+// EXACT arithmetic only.  One thread owns one line; y/z lines are coalesced across lanes (lane =
+// x), x lines are read by one thread each (L1/L2 absorb the 4*bx-byte rows).
+// ------------------------------------------------------------------------------------------
+struct StageParams {
+    float* scratch;        // nb dense blocks
+    long blk_first;        // first block (ticket) of the batch
+    int nb;                // blocks in the batch
+    BlkShape s;
+    int nbx, nby;
+    VolView g;
+};
+
+__global__ void k_stage_gather(const float* __restrict__ vol, const StageParams p)
+{
+    const long B = p.s.B;
+    const long total = (long)p.nb * B;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long k = i / B;
+        const long c = i - k * B;
+        const long t = p.blk_first + k;
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        const int x = (int)(c & (p.s.bx - 1));
+        const long r = c >> p.s.lbx;
+        const int gy = iiy * p.s.by + (int)(r & (p.s.by - 1)), gz = iiz * p.s.bz + (int)(r >> p.s.lby), gx = iix * p.s.bx + x;
+        float v = 0.f;
+        if (gx < p.g.nx && gy < p.g.ny && gz < p.g.nz) v = __ldg(vol + ((long)gz * p.g.ny + gy) * p.g.nx + gx);
+        p.scratch[i] = v;
+    }
+}
+
+__global__ void k_stage_scatter(float* __restrict__ vol, const StageParams p)
+{
+    const long B = p.s.B;
+    const long total = (long)p.nb * B;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long k = i / B;
+        const long c = i - k * B;
+        const long t = p.blk_first + k;
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        const int x = (int)(c & (p.s.bx - 1));
+        const long r = c >> p.s.lbx;
+        const int gy = iiy * p.s.by + (int)(r & (p.s.by - 1)), gz = iiz * p.s.bz + (int)(r >> p.s.lby), gx = iix * p.s.bx + x;
+        if (gx < p.g.nx && gy < p.g.ny && gz < p.g.nz) vol[((long)gz * p.g.ny + gy) * p.g.nx + gx] = p.scratch[i];
+    }
+}
+
+// axis 0: x, 1: y, 2: z.  All levels of one line per thread.
+template <bool FWD>
+__global__ void __launch_bounds__(128) k_stage_pass(float* scratch, int nb, const BlkShape s, int axis)
+{
+    const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
+    const long lines_per_blk = s.B / n;
+    const long total = (long)nb * lines_per_blk;
+    float tmp[256];
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long k = i / lines_per_blk;
+        const long l = i - k * lines_per_blk;
+        float* blk = scratch + k * (long)s.B;
+        long base, stride;
+        if (axis == 0) { base = l * s.bx; stride = 1; }
+        else if (axis == 1) { base = (l >> s.lbx) * ((long)s.bx * s.by) + (l & (s.bx - 1)); stride = s.bx; }
+        else { base = l; stride = (long)s.bx * s.by; }
+        if (FWD) fwd_exact_mem(blk + base, stride, tmp, n);
+        else inv_exact_mem(blk + base, stride, tmp, n);
+    }
+}
+
+constexpr int STAGE_T = 512;
+
+__global__ void __launch_bounds__(STAGE_T, 1) k_stage_encode(const EncParams p, const float* scratch, long blk_first, int nb)
+{
+    __shared__ int4 s_seg[SEG_CAP];
+    __shared__ int scratch_i[72];
+    __shared__ float s_red[32];
+    __shared__ unsigned long long s_off;
+    const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
+    // blocks of the batch are taken in order: CTA b encodes block blk_first + b (+ k * gridDim.x)
+    for (int k = blockIdx.x; k < nb; k += gridDim.x) {
+        const long t = blk_first + k;
+        const float* coef = scratch + (long)k * p.s.B;
+        float mulfac = gmul;
+        if (p.use_local) {
+            float a = 0.f;
+            for (long i = threadIdx.x; i < p.s.B; i += STAGE_T) a = __fmaf_rn(coef[i], coef[i], a);
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+            if (lane_id() == 0) s_red[warp_id()] = a;
+            __syncthreads();
+            float ss = 0.f;
+            for (int w = 0; w < STAGE_T / 32; ++w) ss += s_red[w];
+            __syncthreads();
+            float rms = sqrtf(__fdiv_rn(ss, (float)p.s.B));
+            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+            if (threadIdx.x == 0) p.blkmulfac[t] = mulfac;
+        }
+        auto get8 = [&](int g, float* c) {
+            const float4* q = reinterpret_cast<const float4*>(coef + (long)g * 8);
+            float4 a = q[0], b = q[1];
+            c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+        };
+        encode_tail<STAGE_T>(p, t, coef, mulfac, get8, [](long i) { return i; }, s_seg, scratch_i, &s_off);
+    }
+}
+
+__global__ void __launch_bounds__(STAGE_T, 1) k_stage_decode(const DecParams p, float* scratch, long blk_first, int nb)
+{
+    __shared__ uint32_t s_win[(STAGE_T + 2) * 4];
+    __shared__ int s_ext[STAGE_T];
+    __shared__ int scratch_i[72];
+    for (int k = blockIdx.x; k < nb; k += gridDim.x) {
+        const long t = blk_first + k;
+        float* coef = scratch + (long)k * p.s.B;
+        for (long i = threadIdx.x; i < (p.s.B >> 2); i += STAGE_T) reinterpret_cast<float4*>(coef)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        decode_head<STAGE_T>(p, t, coef, [&](int i, float v) { coef[i] = v; }, [](long i) { return i; }, s_win, s_ext, scratch_i);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Host side: shapes, workspace growth, launchers
+// ------------------------------------------------------------------------------------------
+static int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
+
+bool valid_block_size(int bx, int by, int bz)          // CvxCompress.cpp:54-71 and the asserts :246-248
+{
+    auto p2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
+    if (!p2(bx) || bx < 8 || bx > 256) return false;
+    if (!p2(by) || by < 8 || by > 256) return false;
+    if (bz == 1) return true;
+    return p2(bz) && bz >= 8 && bz <= 256;
+}
+
+bool fused_ok(int bx, int by, int bz)
+{
+    return bx <= 64 && by <= 64 && bz <= 64 && (long)bx * by * bz <= 32768;
+}
+
+Shape make_shape(int nx, int ny, int nz, int bx, int by, int bz)
+{
+    Shape s;
+    s.nx = nx; s.ny = ny; s.nz = nz; s.bx = bx; s.by = by; s.bz = bz;
+    s.nbx = (nx + bx - 1) / bx; s.nby = (ny + by - 1) / by; s.nbz = (nz + bz - 1) / bz;
+    s.nblk = (long)s.nbx * s.nby * s.nbz;
+    return s;
+}
+
+static BlkShape blk_shape(const Shape& s)
+{
+    BlkShape b;
+    b.bx = s.bx; b.by = s.by; b.bz = s.bz;
+    b.lbx = ilog2(s.bx); b.lby = ilog2(s.by);
+    b.B = s.bx * s.by * s.bz;
+    b.sh = b.lbx < 5 ? 5 : b.lbx;
+    return b;
+}
+
+static VolView vol_view(const Shape& s, const void* vol)
+{
+    VolView g;
+    g.nx = s.nx; g.ny = s.ny; g.nz = s.nz;
+    g.vec_ok = ((s.nx & 3) == 0 && (reinterpret_cast<uintptr_t>(vol) & 15) == 0) ? 1 : 0;
+    return g;
+}
+
+cudaError_t ws_reserve_status(cvxgpu_workspace* ws, long nblk)
+{
+    if (nblk <= ws->status_cap) return cudaSuccess;
+    if (ws->d_status) cudaFree(ws->d_status);
+    ws->d_status = nullptr; ws->status_cap = 0;
+    long cap = nblk + nblk / 4 + 1024;
+    cudaError_t e = cudaMalloc(&ws->d_status, sizeof(unsigned long long) * (size_t)cap);
+    if (e == cudaSuccess) ws->status_cap = cap;
+    return e;
+}
+
+cudaError_t ws_reserve_scratch(cvxgpu_workspace* ws, size_t bytes)
+{
+    if (bytes <= ws->scratch_bytes) return cudaSuccess;
+    if (ws->d_scratch) cudaFree(ws->d_scratch);
+    ws->d_scratch = nullptr; ws->scratch_bytes = 0;
+    cudaError_t e = cudaMalloc(&ws->d_scratch, bytes);
+    if (e == cudaSuccess) ws->scratch_bytes = bytes;
+    return e;
+}
+
+cudaError_t launch_sumsq(cvxgpu_workspace* ws, const float* d_vol, long ncells, double* d_sumsq, cudaStream_t st)
+{
+    int grid = ws->n_partial;
+    long need = (ncells / 4 + SUMSQ_T - 1) / SUMSQ_T;
+    if (need < 1) need = 1;
+    if (grid > need) grid = (int)need;
+    k_sumsq<<<grid, SUMSQ_T, 0, st>>>(d_vol, ncells, ws->d_partial);
+    k_sumsq_finish<<<1, 32, 0, st>>>(ws->d_partial, grid, d_sumsq);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int use_local, const double* d_sumsq,
+                                long ncells_total, float* d_mulfac_out, cudaStream_t st)
+{
+    k_write_header<<<1, 32, 0, st>>>(reinterpret_cast<int32_t*>(d_stream), s.nx, s.ny, s.nz, s.bx, s.by, s.bz, scale,
+                                     use_local, d_sumsq, ncells_total, d_mulfac_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finish_length(const long* d_payload_bytes, long table_bytes, long* d_length, cudaStream_t st)
+{
+    k_finish_length<<<1, 32, 0, st>>>(d_payload_bytes, table_bytes, d_length);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_offsets_add(unsigned long long* d_offs, long n, long base, cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    k_offsets_add<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_offs, n, (unsigned long long)base);
+    return cudaGetLastError();
+}
+
+// launch a fused kernel instance with `smem` dynamic bytes on a grid of min(nwork, SMs * occupancy)
+template <class K, class... Args>
+static cudaError_t launch_persistent(K kernel, int T, size_t smem, long nwork, int sm_count, cudaStream_t st, Args... args)
+{
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) return cudaErrorLaunchOutOfResources;
+    long grid = (long)sm_count * occ;
+    if (grid > nwork) grid = nwork;
+    if (grid < 1) return cudaSuccess;
+    kernel<<<(unsigned)grid, T, smem, st>>>(args...);
+    return cudaGetLastError();
+}
+
+// kernel configuration by block shape: a 64-long line needs 255 registers (T = 256); blocks of
+// >= 16384 cells use 512 threads (2 lines per thread and pass at 32^3); small blocks 128 threads
+#define CVX_DISPATCH_FUSED(CALL)                                         \
+    do {                                                                 \
+        const int maxn = s.bx > s.by ? (s.bx > s.bz ? s.bx : s.bz) : (s.by > s.bz ? s.by : s.bz); \
+        const long cells = (long)s.bx * s.by * s.bz;                     \
+        if (maxn == 64) { if (exact) CALL(64, true, 256, 1); else CALL(64, false, 256, 1); }            \
+        else if (cells >= 16384) { if (exact) CALL(32, true, 512, 1); else CALL(32, false, 512, 1); }   \
+        else { if (exact) CALL(32, true, 128, 4); else CALL(32, false, 128, 4); }                        \
+    } while (0)
+
+static void rle_segments(const BlkShape& b, int& nseg, int& gps)
+{
+    int V = b.B / SEG_CAP;
+    if (V < b.bx) V = b.bx;
+    nseg = b.B / V;
+    gps = V / 8;
+}
+
+cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape& s, float scale, int use_local,
+                          const float* d_glob_mulfac, unsigned long long* d_offs, float* d_blkmulfac,
+                          void* d_payload, long cap, long* d_payload_bytes, int* d_err, int exact, cudaStream_t st)
+{
+    cudaError_t e = ws_reserve_status(ws, s.nblk);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(ws->d_status, 0, sizeof(unsigned long long) * (size_t)s.nblk, st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(ws->d_ticket, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) return e;
+    EncParams p;
+    p.vol = d_vol; p.g = vol_view(s, d_vol); p.s = blk_shape(s); p.nbx = s.nbx; p.nby = s.nby; p.nblk = s.nblk;
+    p.scale = scale; p.use_local = use_local; p.glob_mulfac = d_glob_mulfac; p.offs = d_offs; p.blkmulfac = d_blkmulfac;
+    p.payload = reinterpret_cast<uint8_t*>(d_payload); p.cap = cap; p.status = ws->d_status; p.ticket = ws->d_ticket;
+    p.payload_bytes = d_payload_bytes; p.err = d_err;
+    rle_segments(p.s, p.nseg, p.gps);
+    if (fused_ok(s.bx, s.by, s.bz)) {
+        const size_t smem = (size_t)p.s.B * 4 + sizeof(int4) * (size_t)p.nseg;
+#define CVX_CALL_ENC(MAXN, EX, T, MINB) \
+    e = launch_persistent(k_encode_fused<MAXN, EX, T, MINB>, T, smem, s.nblk, ws->sm_count, st, p)
+        CVX_DISPATCH_FUSED(CVX_CALL_ENC);
+#undef CVX_CALL_ENC
+        return e;
+    }
+    // staged: batches of blocks through global scratch
+    const size_t blk_bytes = (size_t)p.s.B * 4;
+    long per_batch = (long)((256ull << 20) / blk_bytes);
+    if (per_batch < 1) per_batch = 1;
+    if (per_batch > s.nblk) per_batch = s.nblk;
+    e = ws_reserve_scratch(ws, blk_bytes * (size_t)per_batch);
+    if (e != cudaSuccess) return e;
+    for (long b0 = 0; b0 < s.nblk; b0 += per_batch) {
+        const int nb = (int)((s.nblk - b0) < per_batch ? (s.nblk - b0) : per_batch);
+        StageParams sp;
+        sp.scratch = ws->d_scratch; sp.blk_first = b0; sp.nb = nb; sp.s = p.s; sp.nbx = s.nbx; sp.nby = s.nby; sp.g = p.g;
+        const long cells = (long)nb * p.s.B;
+        const unsigned g1 = (unsigned)((cells + 255) / 256 < 148L * 64 ? (cells + 255) / 256 : 148L * 64);
+        k_stage_gather<<<g1, 256, 0, st>>>(d_vol, sp);
+        for (int axis = 0; axis < 3; ++axis) {
+            const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
+            if (n < 2) continue;
+            const long lines = cells / n;
+            const unsigned g2 = (unsigned)((lines + 127) / 128);
+            k_stage_pass<true><<<g2, 128, 0, st>>>(ws->d_scratch, nb, p.s, axis);
+        }
+        const int ge = nb < ws->sm_count ? nb : ws->sm_count;
+        k_stage_encode<<<ge, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, float glob_mulfac, int use_local,
+                          const unsigned long long* d_offs, const float* d_blkmulfac, const void* d_payload,
+                          long payload_bytes, int exact, cudaStream_t st)
+{
+    DecParams p;
+    p.vol = d_vol; p.g = vol_view(s, d_vol); p.s = blk_shape(s); p.nbx = s.nbx; p.nby = s.nby; p.nblk = s.nblk;
+    p.glob_mulfac = glob_mulfac; p.use_local = use_local; p.offs = d_offs; p.blkmulfac = d_blkmulfac;
+    p.payload = reinterpret_cast<const uint8_t*>(d_payload); p.payload_bytes = payload_bytes;
+    cudaError_t e = cudaSuccess;
+    if (fused_ok(s.bx, s.by, s.bz)) {
+#define CVX_CALL_DEC(MAXN, EX, T, MINB)                                                   \
+    do {                                                                                  \
+        const size_t smem = (size_t)p.s.B * 4 + (size_t)(T + 2) * 16 + (size_t)T * 4;     \
+        e = launch_persistent(k_decode_fused<MAXN, EX, T, MINB>, T, smem, s.nblk, ws->sm_count, st, p); \
+    } while (0)
+        CVX_DISPATCH_FUSED(CVX_CALL_DEC);
+#undef CVX_CALL_DEC
+        return e;
+    }
+    const size_t blk_bytes = (size_t)p.s.B * 4;
+    long per_batch = (long)((256ull << 20) / blk_bytes);
+    if (per_batch < 1) per_batch = 1;
+    if (per_batch > s.nblk) per_batch = s.nblk;
+    e = ws_reserve_scratch(ws, blk_bytes * (size_t)per_batch);
+    if (e != cudaSuccess) return e;
+    for (long b0 = 0; b0 < s.nblk; b0 += per_batch) {
+        const int nb = (int)((s.nblk - b0) < per_batch ? (s.nblk - b0) : per_batch);
+        const int gd = nb < ws->sm_count * 2 ? nb : ws->sm_count * 2;
+        k_stage_decode<<<gd, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
+        const long cells = (long)nb * p.s.B;
+        for (int axis = 0; axis < 3; ++axis) {
+            const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
+            if (n < 2) continue;
+            const long lines = cells / n;
+            const unsigned g2 = (unsigned)((lines + 127) / 128);
+            k_stage_pass<false><<<g2, 128, 0, st>>>(ws->d_scratch, nb, p.s, axis);
+        }
+        StageParams sp;
+        sp.scratch = ws->d_scratch; sp.blk_first = b0; sp.nb = nb; sp.s = p.s; sp.nbx = s.nbx; sp.nby = s.nby; sp.g = p.g;
+        const unsigned g1 = (unsigned)((cells + 255) / 256 < 148L * 64 ? (cells + 255) / 256 : 148L * 64);
+        k_stage_scatter<<<g1, 256, 0, st>>>(d_vol, sp);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, int bx, int by, int bz, int inverse,
+                           int exact, cudaStream_t st)
+{
+    Shape s = make_shape(bx, by, bz, bx, by, bz);
+    BlkShape b = blk_shape(s);
+    cudaError_t e = cudaSuccess;
+    if (nblocks <= 0) return e;
+    if (fused_ok(bx, by, bz)) {
+        const size_t smem = (size_t)b.B * 4;
+#define CVX_CALL_WAV(MAXN, EX, T, MINB)                                                                             \
+    do {                                                                                                            \
+        if (inverse) e = launch_persistent(k_wavelet_fused<MAXN, EX, false, T, MINB>, T, smem, nblocks, ws->sm_count, st, d_blocks, nblocks, b); \
+        else e = launch_persistent(k_wavelet_fused<MAXN, EX, true, T, MINB>, T, smem, nblocks, ws->sm_count, st, d_blocks, nblocks, b);          \
+    } while (0)
+        CVX_DISPATCH_FUSED(CVX_CALL_WAV);
+#undef CVX_CALL_WAV
+        return e;
+    }
+    // staged, in place on the caller's dense blocks, in batches that keep the int block count small
+    const long per_batch = 1 << 20;
+    for (long b0 = 0; b0 < nblocks; b0 += per_batch) {
+        const int nb = (int)((nblocks - b0) < per_batch ? (nblocks - b0) : per_batch);
+        const long cells = (long)nb * b.B;
+        for (int axis = 0; axis < 3; ++axis) {
+            const int n = axis == 0 ? bx : axis == 1 ? by : bz;
+            if (n < 2) continue;
+            const long lines = cells / n;
+            const unsigned g2 = (unsigned)((lines + 127) / 128);
+            if (inverse) k_stage_pass<false><<<g2, 128, 0, st>>>(d_blocks + b0 * b.B, nb, b, axis);
+            else k_stage_pass<true><<<g2, 128, 0, st>>>(d_blocks + b0 * b.B, nb, b, axis);
+        }
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace cvx

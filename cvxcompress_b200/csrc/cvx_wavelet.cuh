@@ -222,6 +222,15 @@ CVX_HD constexpr int lift_pos_to_idx(int p, int N)
     return N / (2 * s) + (p / s - 1) / 2;
 }
 
+// inverse of lift_pos_to_idx: sub-band index i -> interleaved position
+CVX_HD constexpr int lift_idx_to_pos(int i, int N)
+{
+    if (i == 0) return 0;
+    int h = 1;
+    while (2 * h <= i) h *= 2;
+    return (N / (2 * h)) * (2 * (i - h) + 1);
+}
+
 // ------------------------------------------------------------------------------------------
 // Uniform front end.  v[] holds the line in NATURAL order before fwd / after inv, and in
 // SUB-BAND order after fwd / before inv for EXACT; for LIFT the sub-band side is addressed
@@ -242,6 +251,13 @@ template <int N, bool EXACT>
 CVX_HD constexpr int reg_to_sub(int r)
 {
     return EXACT ? r : lift_pos_to_idx(r, N);
+}
+
+// sub-band index i -> register that holds it
+template <int N, bool EXACT>
+CVX_HD constexpr int sub_to_reg(int i)
+{
+    return EXACT ? i : lift_idx_to_pos(i, N);
 }
 
 // ------------------------------------------------------------------------------------------

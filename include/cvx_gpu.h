@@ -1,0 +1,145 @@
+/*
+ * cvx_gpu.h -- thin C ABI of the B200 (sm_100a) CvxCompress hot path.
+ *
+ * This is the layer the host C++ (`CvxCompress` class, include/CvxCompress.hxx) calls, and the
+ * one an FFI user (ctypes / ccall / cgo) binds when the volume and the stream already live in
+ * device memory.  Plain C types only; `cuda_stream` is a `cudaStream_t` passed as `void*`
+ * (NULL = the legacy default stream).  All `d_*` pointers are DEVICE pointers unless noted.
+ *
+ * Reference interfaces replaced (file:line under ChevronETC/CvxCompress):
+ *   cvxgpu_compress_device     <- CvxCompress::Compress      CvxCompress.cpp:231-427  (decl CvxCompress.hxx:32-45)
+ *   cvxgpu_decompress_device   <- CvxCompress::Decompress    CvxCompress.cpp:463-571  (decl CvxCompress.hxx:105-113)
+ *   cvxgpu_sumsq_device        <- Compute_Global_RMS         CvxCompress.cpp:73-117
+ *   cvxgpu_encode_blocks_device<- the block loop             CvxCompress.cpp:318-420  (Copy_To_Block, Wavelet_Transform_Fast_Forward,
+ *                                                            Compute_Local_RMS, Run_Length_Encode_Slow, raw fallback, offset table)
+ *   cvxgpu_decode_blocks_device<- the block loop             CvxCompress.cpp:528-568  (Run_Length_Decode_Slow, Wavelet_Transform_Fast_Inverse,
+ *                                                            Copy_From_Block)
+ *   cvxgpu_write_header_device <- header words 0..7          CvxCompress.cpp:284-300
+ *   cvxgpu_is_valid_block_size <- Is_Valid_Block_Size        CvxCompress.cpp:54-71
+ *   cvxgpu_wavelet_blocks_device <- Wavelet_Transform_Fast_{Forward,Inverse} on an array of dense blocks
+ *                                                            (the module-test sweep, CvxCompress.cpp:803-891)
+ *
+ * Stream format (identical to the reference): 32-byte header, int64 offset per
+ * block (bit 63 = raw block), optional fp32 mulfac per block, payload; length = 32 + 8*nnn
+ * [+ 4*nnn] + payload_bytes + 7.  Blocks are laid out in natural iBlk order (what the reference
+ * produces with num_threads=1).
+ *
+ * Every function returns CVXGPU_OK (0) or a negative error code; cvxgpu_last_error() gives the
+ * message of the calling thread's last failure.  There is NO CPU fallback: without a CUDA
+ * device every compute entry point fails with CVXGPU_ERR_CUDA.
+ */
+#ifndef CVX_GPU_H
+#define CVX_GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CVXGPU_OK 0
+#define CVXGPU_ERR_ARG (-1)       /* bad dimension / block size / null pointer          */
+#define CVXGPU_ERR_CUDA (-2)      /* CUDA runtime failure (message has the CUDA error)  */
+#define CVXGPU_ERR_CAPACITY (-3)  /* stream would not fit in `capacity` bytes           */
+#define CVXGPU_ERR_STREAM (-4)    /* malformed / mismatching compressed stream          */
+
+/* arithmetic of the 9/7 transform.  EXACT = direct-form filter bank in the reference's operation
+ * order (bit-identical coefficients and streams); LIFTING = 4-step lifting with FMA (same
+ * operator, ~4e-7 rms-relative coefficient difference, 2.3x fewer FP32 instructions). */
+#define CVXGPU_TRANSFORM_EXACT 0
+#define CVXGPU_TRANSFORM_LIFTING 1
+
+typedef struct cvxgpu_workspace cvxgpu_workspace;
+
+const char* cvxgpu_last_error(void);
+int  cvxgpu_device_count(void);
+
+/* process-wide default transform (initialised from env CVX_GPU_TRANSFORM=exact|lifting; default exact) */
+int  cvxgpu_set_transform(int mode);
+int  cvxgpu_get_transform(void);
+
+/* scratch owned by the caller: look-back status words, partial sums, staging.  One workspace
+ * must not be used by two host threads at once.  NULL may be passed to every call below, in
+ * which case a per-host-thread default workspace on the current device is used. */
+int  cvxgpu_workspace_create(cvxgpu_workspace** ws);
+int  cvxgpu_workspace_destroy(cvxgpu_workspace* ws);
+
+int  cvxgpu_is_valid_block_size(int bx, int by, int bz);
+long cvxgpu_num_blocks(int nx, int ny, int nz, int bx, int by, int bz);
+/* worst case (every block raw): 32 + 8*nnn [+ 4*nnn] + 4*bx*by*bz*nnn + 7 */
+long cvxgpu_max_compressed_bytes(int nx, int ny, int nz, int bx, int by, int bz, int use_local_rms);
+
+/* ---- whole-volume calls (one GPU) ------------------------------------------------------- */
+
+/* Compress d_vol (nx fastest, nz slowest) into d_stream.  *length receives compressed_length,
+ * *ratio the reference's return value 4*N/length.  Synchronises `cuda_stream` before returning
+ * (the length is an output).  d_stream must be 8-byte aligned. */
+int cvxgpu_compress_device(cvxgpu_workspace* ws, const float* d_vol, int nx, int ny, int nz,
+                           int bx, int by, int bz, float scale, int use_local_rms,
+                           void* d_stream, long capacity, long* length, float* ratio, void* cuda_stream);
+
+/* Same work, no host synchronisation: the length is left in *d_length (device int64) and an
+ * overflow / error code in *d_status (device int32, 0 = ok).  Used by bench.py's device-resident
+ * timing and by callers that keep everything on a stream. */
+int cvxgpu_compress_device_async(cvxgpu_workspace* ws, const float* d_vol, int nx, int ny, int nz,
+                                 int bx, int by, int bz, float scale, int use_local_rms,
+                                 void* d_stream, long capacity, long* d_length, int* d_status, void* cuda_stream);
+
+/* Decompress d_stream into d_vol.  nx,ny,nz must match the header (the reference prints and
+ * asserts, CvxCompress.cpp:473-488; here CVXGPU_ERR_STREAM).  Asynchronous on `cuda_stream`
+ * apart from a 32-byte header read. */
+int cvxgpu_decompress_device(cvxgpu_workspace* ws, float* d_vol, int nx, int ny, int nz,
+                             const void* d_stream, long length, void* cuda_stream);
+
+/* header fields of a stream held in HOST memory (no GPU needed) */
+int cvxgpu_parse_header(const void* h_stream, long length, int* nx, int* ny, int* nz,
+                        int* bx, int* by, int* bz, float* glob_mulfac, int* flags);
+
+/* ---- host-pointer convenience (what the CvxCompress class calls) ---------------------------
+ * `vol` / `stream` may be pageable host, pinned host, managed or device pointers
+ * (cudaPointerGetAttributes); host memory is staged through pinned chunks. */
+int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx, int by, int bz, float scale,
+                    int use_local_rms, void* stream_out, long* length, float* ratio);
+int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void* stream_in, long length);
+
+/* ---- pieces, for z-slab sharding over several GPUs --------------------------
+ * A rank owns the block rows [blkz0, blkz1) of the volume: a contiguous iBlk range and a
+ * contiguous z-slab of memory.  Sequence on every rank:
+ *   cvxgpu_sumsq_device(slab)                     -> d_sumsq (device double)
+ *   all-gather the doubles, add them in rank order -> d_sumsq_total       (NCCL, 8 bytes/rank)
+ *   cvxgpu_encode_blocks_device(slab, ...)        -> slab table slice + slab payload, local offsets
+ *   all-gather payload byte counts                -> this rank's base     (NCCL, 8 bytes/rank)
+ *   cvxgpu_offsets_add_device(slice, base)
+ * Decompress needs no collective: every rank decodes its own iBlk range from the full stream. */
+int cvxgpu_sumsq_device(cvxgpu_workspace* ws, const float* d_vol, long ncells, double* d_sumsq, void* cuda_stream);
+
+/* Encode the blocks of a volume (or slab) of nx*ny*nz_slab cells.  d_sumsq_total / ncells_total
+ * define the global RMS (ignored when use_local_rms).  d_offs receives nblk entries (payload
+ * offsets relative to d_payload, bit 63 = raw), d_blkmulfac nblk floats when use_local_rms (else
+ * may be NULL), *d_payload_bytes the payload size, *d_status 0 or CVXGPU_ERR_CAPACITY. */
+int cvxgpu_encode_blocks_device(cvxgpu_workspace* ws, const float* d_vol, int nx, int ny, int nz_slab,
+                                int bx, int by, int bz, float scale, int use_local_rms,
+                                const double* d_sumsq_total, long ncells_total,
+                                unsigned long long* d_offs, float* d_blkmulfac,
+                                void* d_payload, long payload_capacity,
+                                long* d_payload_bytes, int* d_status, void* cuda_stream);
+
+int cvxgpu_write_header_device(void* d_stream, int nx, int ny, int nz, int bx, int by, int bz, float scale,
+                               int use_local_rms, const double* d_sumsq_total, long ncells_total, void* cuda_stream);
+
+int cvxgpu_offsets_add_device(unsigned long long* d_offs, long n, long base, void* cuda_stream);
+
+/* Decode blocks [blk_first, blk_first + nblk_slab) of the full stream d_stream (nx,ny,nz and
+ * block sizes come from its header, which is passed in by value to avoid a device read) into
+ * the slab d_vol_slab whose first plane is z = (blk_first / (nbx*nby)) * bz. */
+int cvxgpu_decode_blocks_device(cvxgpu_workspace* ws, float* d_vol_slab, int nx, int ny, int nz_slab,
+                                int bx, int by, int bz, float glob_mulfac, int use_local_rms,
+                                const unsigned long long* d_offs, const float* d_blkmulfac,
+                                const void* d_payload, long payload_bytes, void* cuda_stream);
+
+/* ---- wavelet only: nblocks dense blocks (x fastest), in place (config 2 sweep) ------------- */
+int cvxgpu_wavelet_blocks_device(cvxgpu_workspace* ws, float* d_blocks, long nblocks, int bx, int by, int bz,
+                                 int inverse, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,298 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the
+oracle (oracle/libcvx_oracle.so) and -- when it travelled -- the unmodified reference build
+(oracle/_ref).  Bit-exact for streams, coefficients and reconstructions in EXACT mode; stated
+tolerances for LIFTING mode."""
+import ctypes as C
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_libs as ol
+from cvxcompress_b200 import synth
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import torch
+    from cvxcompress_b200 import _lib, api
+    assert torch.cuda.is_available()
+    L = _lib.lib()          # raises if the CUDA library is missing: no fallback
+    assert L.cvxgpu_device_count() >= 1
+    api.set_transform("exact")
+    return api
+
+
+def _gpu_compress(api, vol, bx, by, bz, scale, local=False):
+    import torch
+    d = torch.from_numpy(np.ascontiguousarray(vol)).cuda()
+    out, ln, ratio = api.compress_device(d, bx, by, bz, scale, local)
+    return out[:ln].cpu().numpy().copy(), ratio
+
+
+def _gpu_decompress(api, stream, nx, ny, nz):
+    import torch
+    s = torch.zeros(len(stream) + 64, dtype=torch.uint8, device="cuda")
+    s[:len(stream)] = torch.from_numpy(np.ascontiguousarray(stream)).cuda()
+    return api.decompress_device(s, len(stream), nx, ny, nz).cpu().numpy()
+
+
+def _vol(kind, nx, ny, nz, seed=1):
+    if kind == "g1":
+        return synth.g1(nx, ny, nz)
+    if kind == "g2":
+        return synth.g2(nx, ny, nz)
+    if kind == "noise":
+        return synth.g3(nx * ny * nz, seed=seed, lo=-1.0, hi=1.0).reshape(nz, ny, nx)
+    if kind == "zero":
+        return np.zeros((nz, ny, nx), np.float32)
+    if kind == "big":       # large dynamic range: VLESC3 / VLESC4 / *_8x tokens
+        v = synth.g3(nx * ny * nz, seed=seed, lo=-1.0, hi=1.0).reshape(nz, ny, nx)
+        return (v * np.float32(3e4) * (1 + 100 * (v > 0.9))).astype(np.float32)
+    raise KeyError(kind)
+
+
+def _streams_equal(a, b):
+    """Everything the library writes: [0, length-7) (the 7 slack bytes are never written)."""
+    return len(a) == len(b) and bytes(a[:len(a) - 7]) == bytes(b[:len(b) - 7])
+
+
+CASES = [
+    # kind, nx, ny, nz, bx, by, bz, scale
+    ("g2", 64, 64, 64, 32, 32, 32, 1e-2),
+    ("g2", 151, 101, 51, 32, 32, 32, 1e-2),          # partial blocks in x, y, z
+    ("g2", 151, 101, 51, 16, 16, 64, 1e-3),
+    ("g2", 37, 41, 43, 8, 8, 8, 1e-2),               # nx not a multiple of 4 (scalar gather path)
+    ("g2", 160, 96, 5, 32, 32, 1, 1e-2),             # 2-D mode
+    ("g2", 100, 70, 40, 16, 16, 16, 1e-4),
+    ("g2", 96, 64, 48, 32, 16, 8, 1e-3),
+    ("g2", 96, 64, 48, 8, 32, 16, 1e-3),
+    ("g2", 70, 130, 64, 64, 64, 8, 1e-3),            # 64-long lines (255-register kernels)
+    ("g2", 64, 64, 70, 8, 8, 64, 1e-3),
+    ("noise", 64, 64, 64, 32, 32, 32, 1e-5),         # ratio ~1.3, long literal stretches
+    ("noise", 64, 64, 64, 32, 32, 32, 1e-9),         # every block raw
+    ("noise", 72, 40, 40, 16, 16, 16, 3e-7),         # mix of raw and coded blocks
+    ("big", 64, 64, 32, 32, 32, 32, 1e-6),           # VLESC3/VLESC4 and the 8x group codes
+    ("zero", 64, 64, 64, 32, 32, 32, 1e-2),          # rms == 0 -> mulfac 1, one RLESC3 per block
+    ("g1", 352, 416, 32, 32, 32, 32, 1e-2),
+    ("g2", 300, 20, 20, 256, 8, 8, 1e-3),            # staged path (a dimension > 64)
+    ("g2", 130, 130, 70, 128, 128, 64, 1e-3),        # staged path, 1 Mi-cell blocks
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_stream_identical_to_oracle_global_rms(gpu, case):
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    vol = _vol(kind, nx, ny, nz)
+    want, want_ratio = ol.oracle_compress(vol, bx, by, bz, scale, False)
+    got, ratio = _gpu_compress(gpu, vol, bx, by, bz, scale, False)
+    assert len(got) == len(want)
+    assert _streams_equal(got, want)
+    assert ratio == pytest.approx(want_ratio, rel=1e-6)
+    # the GPU decodes its own stream to exactly what the oracle decodes
+    a = _gpu_decompress(gpu, got, nx, ny, nz)
+    b = ol.oracle_decompress(want, nx, ny, nz)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+@pytest.mark.parametrize("case", [c for c in CASES if c[0] in ("g2", "noise")][:9], ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_local_rms(gpu, case):
+    """Local RMS: blkmulfac is a parallel fp32 reduction here and 8 serial lanes in the reference
+    (CvxCompress.cpp:119-142), so it may differ in the last bits; everything downstream of an equal
+    mulfac is exact, and each decoder must reproduce the other's reconstruction of the same stream."""
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    vol = _vol(kind, nx, ny, nz)
+    want, _ = ol.oracle_compress(vol, bx, by, bz, scale, True)
+    got, _ = _gpu_compress(gpu, vol, bx, by, bz, scale, True)
+    sw, sg = ol.parse_stream(want), ol.parse_stream(got)
+    assert sg["flags"] == 1 and sg["mulfac"] == sw["mulfac"]
+    np.testing.assert_allclose(sg["blkmulfac"], sw["blkmulfac"], rtol=2e-6)
+    assert abs(len(got) - len(want)) <= max(64, len(want) // 1000)
+    # cross decode, both directions, bit-exact
+    a = _gpu_decompress(gpu, want, nx, ny, nz)
+    b = ol.oracle_decompress(want, nx, ny, nz)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    c = _gpu_decompress(gpu, got, nx, ny, nz)
+    d = ol.oracle_decompress(got, nx, ny, nz)
+    assert np.array_equal(c.view(np.uint32), d.view(np.uint32))
+    e1, _ = synth.quality(vol, c)
+    e2, _ = synth.quality(vol, b)
+    assert e1 == pytest.approx(e2, rel=1e-3, abs=1e-9)
+
+
+@pytest.mark.skipif(not ol.have_ref(), reason="oracle/_ref (reference build) did not travel")
+@pytest.mark.parametrize("case", [CASES[1], CASES[2], CASES[5], CASES[10]], ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_interop_with_reference_build(gpu, case):
+    """The unmodified reference decodes the GPU stream; the GPU decodes a reference stream written
+    by 8 threads (permuted block order, CvxCompress.cpp:365-390)."""
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    vol = _vol(kind, nx, ny, nz)
+    got, _ = _gpu_compress(gpu, vol, bx, by, bz, scale, False)
+    ref1, _ = ol.ref_compress(vol, bx, by, bz, scale, False, threads=1)
+    assert _streams_equal(got, ref1)
+    ref8, _ = ol.ref_compress(vol, bx, by, bz, scale, False, threads=8)
+    a = ol.ref_decompress(got, nx, ny, nz, threads=4)
+    b = ol.ref_decompress(ref8, nx, ny, nz, threads=4)
+    c = _gpu_decompress(gpu, ref8, nx, ny, nz)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert np.array_equal(c.view(np.uint32), b.view(np.uint32))
+
+
+def test_golden_config1(gpu):
+    """Test_With_Generated_Input.cpp:21-51 / README.md:72-81: 352x416x320, 32^3, scale 1e-2 -> 178789 bytes,
+    ratio 1048.35, error 1.663531e-04, SNR 75.6 dB (asserts error < 2e-4, snr > 75, :121-122)."""
+    vol = synth.g1(352, 416, 320)
+    got, ratio = _gpu_compress(gpu, vol, 32, 32, 32, 1e-2, False)
+    assert len(got) == 178789
+    assert ratio == pytest.approx(1048.35, abs=0.01)
+    with open(os.path.join(HERE, "golden", "golden.json")) as f:
+        g = json.load(f)["c1_g1_352x416x320_b32_s1e-2"]
+    assert hashlib.sha256(bytes(got[:len(got) - 7])).hexdigest() == g["sha256_written"]
+    rec = _gpu_decompress(gpu, got, 352, 416, 320)
+    err, snr = synth.quality(vol, rec)
+    assert err < 2e-4 and snr > 75.0
+    assert err == pytest.approx(1.663531e-04, rel=1e-5)
+    assert hashlib.sha256(rec.tobytes()).hexdigest() == g["sha256_decoded"]
+
+
+@pytest.mark.parametrize("shape", [(8, 8, 8), (16, 16, 16), (32, 32, 32), (16, 16, 64), (32, 32, 1), (64, 64, 8), (8, 32, 16),
+                                   (128, 8, 8), (8, 8, 256)])
+def test_wavelet_blocks_exact_bitwise(gpu, shape):
+    """EXACT transform == Wavelet_Transform_Fast (oracle FAST association) bit for bit; and within 1e-6 of the
+    block magnitude of Wavelet_Transform_Slow (north_star; the reference's own criterion is rms-rel 1e-5)."""
+    import torch
+    bx, by, bz = shape
+    B = bx * by * bz
+    nb = 5
+    blocks = synth.g3(nb * B, seed=3 + B, lo=-1.0, hi=1.0)
+    d = torch.from_numpy(blocks.copy()).cuda()
+    gpu.wavelet_blocks_device(d, bx, by, bz, inverse=False)
+    fwd = d.cpu().numpy()
+    for k in range(nb):
+        a = blocks[k * B:(k + 1) * B].copy()
+        ol.oracle().cvxo_wavelet_forward(a, bx, by, bz, 0)
+        assert np.array_equal(a.view(np.uint32), fwd[k * B:(k + 1) * B].view(np.uint32))
+        s = blocks[k * B:(k + 1) * B].copy()
+        ol.oracle().cvxo_wavelet_forward(s, bx, by, bz, 1)
+        assert np.abs(s - fwd[k * B:(k + 1) * B]).max() <= 1e-6 * np.abs(s).max()
+    gpu.wavelet_blocks_device(d, bx, by, bz, inverse=True)
+    inv = d.cpu().numpy()
+    for k in range(nb):
+        a = fwd[k * B:(k + 1) * B].copy()
+        ol.oracle().cvxo_wavelet_inverse(a, bx, by, bz, 0)
+        assert np.array_equal(a.view(np.uint32), inv[k * B:(k + 1) * B].view(np.uint32))
+    assert np.abs(inv - blocks).max() < 2e-6
+
+
+@pytest.mark.parametrize("shape", [(8, 8, 8), (16, 16, 16), (32, 32, 32), (16, 16, 64), (32, 32, 1)])
+def test_wavelet_blocks_lifting_tolerance(gpu, shape):
+    import torch
+    bx, by, bz = shape
+    B = bx * by * bz
+    blocks = synth.g3(4 * B, seed=11 + B, lo=-1.0, hi=1.0)
+    gpu.set_transform("lifting")
+    try:
+        d = torch.from_numpy(blocks.copy()).cuda()
+        gpu.wavelet_blocks_device(d, bx, by, bz, inverse=False)
+        fwd = d.cpu().numpy()
+        gpu.wavelet_blocks_device(d, bx, by, bz, inverse=True)
+        inv = d.cpu().numpy()
+    finally:
+        gpu.set_transform("exact")
+    for k in range(4):
+        s = blocks[k * B:(k + 1) * B].copy()
+        ol.oracle().cvxo_wavelet_forward(s, bx, by, bz, 1)
+        g = fwd[k * B:(k + 1) * B]
+        rms_rel = np.sqrt(np.mean((g - s).astype(np.float64) ** 2)) / np.sqrt(np.mean(s.astype(np.float64) ** 2))
+        assert rms_rel < 1e-6                                   # reference criterion is 1e-5 (CvxCompress.cpp:597)
+        assert np.abs(g - s).max() <= 2e-6 * np.abs(s).max()    # north_star: 1e-6 relative, read against the block magnitude
+    assert np.abs(inv - blocks).max() < 3e-6
+
+
+@pytest.mark.parametrize("case", [CASES[1], CASES[2], CASES[0]], ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_lifting_mode_quality_and_interop(gpu, case):
+    """LIFTING: stream decodes with the oracle (reference decoder), ratio within 0.5 %, SNR within 0.1 dB."""
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    vol = _vol(kind, nx, ny, nz)
+    want, want_ratio = ol.oracle_compress(vol, bx, by, bz, scale, False)
+    ref_rec = ol.oracle_decompress(want, nx, ny, nz)
+    gpu.set_transform("lifting")
+    try:
+        got, ratio = _gpu_compress(gpu, vol, bx, by, bz, scale, False)
+        rec_gpu = _gpu_decompress(gpu, got, nx, ny, nz)
+        rec_gpu_of_ref = _gpu_decompress(gpu, want, nx, ny, nz)
+    finally:
+        gpu.set_transform("exact")
+    rec_ref_of_gpu = ol.oracle_decompress(got, nx, ny, nz)
+    assert ratio == pytest.approx(want_ratio, rel=5e-3)
+    _, snr_ref = synth.quality(vol, ref_rec)
+    for rec in (rec_gpu, rec_gpu_of_ref, rec_ref_of_gpu):
+        _, snr = synth.quality(vol, rec)
+        assert abs(snr - snr_ref) < 0.1
+
+
+def test_host_pointer_class_api(gpu):
+    """The reference-facing entry points with HOST buffers (cvx_compress_th / cvx_decompress_inplace_th,
+    CvxCompress.hxx:169-192), exactly as Test_With_Generated_Input.cpp:73-90 calls them."""
+    nx, ny, nz = 151, 101, 51
+    vol = synth.g2(nx, ny, nz)
+    c = gpu.CvxCompress()
+    want, want_ratio = ol.oracle_compress(vol, 32, 32, 32, 1e-2, False)
+    buf = np.zeros(vol.size, dtype=np.uint8)      # the reference test allocates only N bytes (Test_With_Generated_Input.cpp:39)
+    buf[:] = 0xAB
+    ratio, ln = c.Compress(1e-2, vol, nx, ny, nz, 32, 32, 32, False, buf, 4)
+    assert ln == len(want) and _streams_equal(buf[:ln], want)
+    assert np.all(buf[ln - 7:] == 0xAB)           # nothing beyond length-7 is written
+    assert ratio == pytest.approx(want_ratio, rel=1e-6)
+    out = np.empty((nz, ny, nx), np.float32)
+    c.Decompress(out, nx, ny, nz, buf, ln)
+    assert np.array_equal(out.view(np.uint32), ol.oracle_decompress(want, nx, ny, nz).view(np.uint32))
+    out2, x, y, z = c.Decompress_outofplace(buf, ln)
+    assert (x, y, z) == (nx, ny, nz) and np.array_equal(out2, out)
+    with pytest.raises(ValueError):
+        c.Decompress(np.empty((nz, ny, nx + 1), np.float32), nx + 1, ny, nz, buf, ln)
+    with pytest.raises(ValueError):
+        c.Compress(1e-2, vol, nx, ny, nz, 24, 32, 32, False, buf)
+
+
+def test_capacity_error_and_bad_args(gpu):
+    import torch
+    from cvxcompress_b200 import _lib
+    vol = torch.from_numpy(_vol("noise", 64, 64, 64)).cuda()
+    small = torch.empty(4096, dtype=torch.uint8, device="cuda")
+    with pytest.raises(_lib.CvxError) as e:
+        gpu.compress_device(vol, 32, 32, 32, 1e-5, False, out=small)
+    assert e.value.code == _lib.ERR_CAPACITY
+    with pytest.raises(ValueError):
+        gpu.max_compressed_bytes(64, 64, 64, 12, 32, 32)
+    s, ln, _ = gpu.compress_device(vol, 32, 32, 32, 1e-2)
+    with pytest.raises(_lib.CvxError) as e:
+        gpu.decompress_device(s, ln, 64, 64, 32)
+    assert e.value.code == _lib.ERR_STREAM
+
+
+def test_full_size_config3_golden_length_and_roundtrip(gpu):
+    """BASELINE config 3 (960x1248x1056 fp32 = nx,ny,nz 1056,1248,960; 32^3; global RMS): README.md:91-99 golden length
+    4 826 289 bytes, ratio 1048.57, SNR 75.6 dB; plus size-independent properties at full size: idempotent
+    re-compression of the stream length, decode(compress(v)) error bound, determinism."""
+    import torch
+    nx, ny, nz = 1056, 1248, 960
+    vol = synth.g1_torch(nx, ny, nz, "cuda")
+    s, ln, ratio = gpu.compress_device(vol, 32, 32, 32, 1e-2)
+    assert ln == 4826289
+    assert ratio == pytest.approx(1048.57, abs=0.01)
+    rec = gpu.decompress_device(s, ln, nx, ny, nz)
+    num = torch.sqrt(torch.mean((vol.double() - rec.double()) ** 2)).item()
+    den = torch.sqrt(torch.mean(vol.double() ** 2)).item()
+    err = num / den
+    assert err == pytest.approx(1.663531e-04, rel=1e-4)
+    assert -20 * np.log10(err) > 75.0
+    s2, ln2, _ = gpu.compress_device(vol, 32, 32, 32, 1e-2)
+    assert ln2 == ln and torch.equal(s[:ln - 7], s2[:ln - 7])          # deterministic, natural block order
+    offs = s[32:32 + 8 * 38610].view(torch.int64)
+    assert bool((offs[1:] > offs[:-1]).all())                          # sorted offsets == natural order
