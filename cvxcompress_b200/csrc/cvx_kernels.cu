@@ -289,6 +289,30 @@ __device__ __forceinline__ void scatter_block(const float* sm, float* __restrict
 // sum of squares of the block's coefficients over the CTA (Compute_Local_RMS, CvxCompress.cpp:119-142;
 // the summation order differs from the reference's 8 serial lanes, so blkmulfac may differ in the
 // last bits -- the value travels in the stream, so decoding is unaffected)
+// EXACT: the reference's own order -- 8 lanes, lane j adds c[8i+j]^2 serially (mul then add, no FMA:
+// the shipped build is -mavx only), then ((a0+a1)+(a2+a3)) + ((a4+a5)+(a6+a7)) from the two hadd
+// steps and the 128-bit halves add (CvxCompress.cpp:124-139).  Bit-identical blkmulfac, at the cost
+// of a serial chain of B/8 dependent FADDs on 8 threads.  `get` maps a raster index to the value.
+template <int T, class Get>
+__device__ __forceinline__ float cta_sumsq_exact(int B, float* s_red, Get get)
+{
+    if (threadIdx.x < 8) {
+        float acc = 0.f;
+        const int n = B >> 3;
+#pragma unroll 8
+        for (int i = 0; i < n; ++i) {
+            float v = get(8 * i + (int)threadIdx.x);
+            acc = __fadd_rn(acc, __fmul_rn(v, v));
+        }
+        s_red[threadIdx.x] = acc;
+    }
+    __syncthreads();
+    const float lo = __fadd_rn(__fadd_rn(s_red[0], s_red[1]), __fadd_rn(s_red[2], s_red[3]));
+    const float hi = __fadd_rn(__fadd_rn(s_red[4], s_red[5]), __fadd_rn(s_red[6], s_red[7]));
+    __syncthreads();
+    return __fadd_rn(lo, hi);
+}
+
 template <int T>
 __device__ __forceinline__ float cta_sumsq(const float* sm, int B, float* s_red)
 {
@@ -402,7 +426,9 @@ __global__ void __launch_bounds__(T, MINB) k_encode_fused(const EncParams p)
         transform_block<MAXN, EXACT, true, T>(sm, s);
         float mulfac = gmul;
         if (p.use_local) {
-            float ss = cta_sumsq<T>(sm, s.B, s_red);
+            const int shl = s.sh;
+            float ss = EXACT ? cta_sumsq_exact<T>(s.B, s_red, [&](int i) { return sm[physr(i, shl)]; })
+                             : cta_sumsq<T>(sm, s.B, s_red);
             float rms = sqrtf(__fdiv_rn(ss, (float)s.B));
             mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;     // CvxCompress.cpp:346
             if (threadIdx.x == 0) p.blkmulfac[t] = mulfac;
@@ -598,15 +624,8 @@ __global__ void __launch_bounds__(STAGE_T, 1) k_stage_encode(const EncParams p, 
         const float* coef = scratch + (long)k * p.s.B;
         float mulfac = gmul;
         if (p.use_local) {
-            float a = 0.f;
-            for (long i = threadIdx.x; i < p.s.B; i += STAGE_T) a = __fmaf_rn(coef[i], coef[i], a);
-#pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
-            if (lane_id() == 0) s_red[warp_id()] = a;
-            __syncthreads();
-            float ss = 0.f;
-            for (int w = 0; w < STAGE_T / 32; ++w) ss += s_red[w];
-            __syncthreads();
+            // the staged path is EXACT arithmetic throughout: the reference's summation order
+            float ss = cta_sumsq_exact<STAGE_T>(p.s.B, s_red, [&](int i) { return __ldg(coef + i); });
             float rms = sqrtf(__fdiv_rn(ss, (float)p.s.B));
             mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
             if (threadIdx.x == 0) p.blkmulfac[t] = mulfac;

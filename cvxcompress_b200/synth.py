@@ -44,6 +44,17 @@ def g2(nx, ny, nz, seed=SEED):
     return (np.sin(r / 10.0) + uniform01_np(idx, seed) / 100.0).astype(np.float32)
 
 
+def g2_slab(nx, ny, nz, z0=0, nz_total=None, seed=SEED):
+    """z-slab [z0, z0+nz) of the nz_total-deep G2 volume (same cells as g2(nx, ny, nz_total)[z0:z0+nz])."""
+    nzt = nz if nz_total is None else nz_total
+    z = np.arange(z0, z0 + nz, dtype=np.float64)[:, None, None] - (nzt - 1) / 2.0
+    y = np.arange(ny, dtype=np.float64)[None, :, None] - (ny - 1) / 2.0
+    x = np.arange(nx, dtype=np.float64)[None, None, :] - (nx - 1) / 2.0
+    r = np.sqrt(x * x + y * y + z * z)
+    idx = (np.arange(nx * ny * nz, dtype=np.uint64) + np.uint64(z0 * nx * ny)).reshape(nz, ny, nx)
+    return (np.sin(r / 10.0) + uniform01_np(idx, seed) / 100.0).astype(np.float32)
+
+
 def g3(n, seed=SEED, lo=0.0, hi=1.0):
     idx = np.arange(n, dtype=np.uint64)
     return (lo + (hi - lo) * uniform01_np(idx, seed)).astype(np.float32)
