@@ -1,0 +1,222 @@
+// cvx_encode32.inl -- k_encode32, included by cvx_kernels.cu inside namespace cvx after EncParams,
+// gather_block, cta_sumsq*, encode_tail (design notes: cvx_fused32.cuh).
+
+// publish this block's byte count in ticket order, fill its table entry, return its payload offset (warp 0, all lanes)
+__device__ __forceinline__ unsigned long long place_block(const EncParams& p, long t, unsigned long long nbytes, bool raw)
+{
+    const unsigned long long excl = lookback_exclusive(p.status, t, nbytes);
+    if (lane_id() == 0) {
+        p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);              // CvxCompress.cpp:382-384
+        if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + nbytes);
+    }
+    return excl;
+}
+
+template <bool EXACT>
+__global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ CUtensorMap tmap, const EncParams p, const int use_tma)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    uint32_t* s_nzm = reinterpret_cast<uint32_t*>(smem_raw + F32_OFF_NZM);
+    int* s_base = reinterpret_cast<int*>(smem_raw + F32_OFF_BASE);
+    uint2* s_list = reinterpret_cast<uint2*>(smem_raw + F32_OFF_LIST);
+    unsigned char* s_stage = smem_raw + F32_OFF_STAGE;
+    __shared__ uint64_t s_bar;
+    __shared__ int scratch[72];
+    __shared__ float s_red[32];
+    __shared__ unsigned int s_ticket[2];
+    __shared__ unsigned long long s_off;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const BlkShape s = p.s;
+    const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
+
+    auto issue_load = [&](unsigned int t) {      // one thread: TMA of block t into the block buffer, 4 boxes of 32x32x8
+        const int iix = (int)(t % p.nbx);
+        const unsigned int q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        mbar_expect_tx(&s_bar, F32_B * 4);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) tma_load_3d(sm + b * 8192, &tmap, &s_bar, iix * 32, iiy * 32, iiz * 32 + b * 8);
+    };
+
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        const unsigned int t0 = atomicAdd(p.ticket, 1u);
+        s_ticket[0] = t0;
+        if (use_tma && t0 < p.nblk) { fence_proxy_async(); issue_load(t0); }
+    }
+    __syncthreads();
+
+    uint32_t parity = 0;
+    for (int it = 0;; ++it) {
+        const long t = s_ticket[it & 1];
+        if (t >= p.nblk) break;
+        if (use_tma) {
+            mbar_wait(&s_bar, parity);
+            parity ^= 1u;
+        } else {
+            const int iix = (int)(t % p.nbx);
+            const long q = t / p.nbx;
+            gather_block<F32_T>(sm, p.vol, p.g, iix * 32, (int)(q % p.nby) * 32, (int)(q / p.nby) * 32, s);
+            __syncthreads();
+        }
+        f32_pass_x<EXACT, true>(sm);
+        __syncthreads();
+        f32_pass_y<EXACT, true>(sm);
+        __syncthreads();
+        // z lines stay in registers: thread-line l = tid + 512 k is (x = lane, y = warp + 16 k)
+        float v[2][32];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float* zl = f32_zline(sm, tid + F32_T * k);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[k][j] = zl[j * 1024];
+            fwd_line<32, EXACT>(v[k]);
+        }
+        auto write_back = [&]() {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                float* zl = f32_zline(sm, tid + F32_T * k);
+#pragma unroll
+                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = v[k][r];
+            }
+        };
+        bool in_smem = false;
+        float mulfac = gmul;
+        if (p.use_local) {                                       // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348
+            __syncthreads();
+            write_back();
+            in_smem = true;
+            __syncthreads();
+            const float ss = EXACT ? cta_sumsq_exact<F32_T>(F32_B, s_red, [&](int i) { return sm[physr(i, 5)]; })
+                                   : cta_sumsq<F32_T>(sm, F32_B, s_red);
+            const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
+            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+            if (tid == 0) p.blkmulfac[t] = mulfac;
+        }
+        // ---- which coefficients quantise to non-zero: one compare per cell, one ballot per row ----
+        const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
+        int n = F32_LCAP + 1;
+        if (sparse_ok) {
+            const float T = nz_threshold(mulfac);
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(v[k][r]) <= T));
+                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+                }
+            __syncthreads();
+            const int c0 = __popc(s_nzm[2 * tid]), c1 = __popc(s_nzm[2 * tid + 1]);
+            const int base = cta_excl_sum<F32_T>(c0 + c1, scratch, n);
+            s_base[2 * tid] = base;
+            s_base[2 * tid + 1] = base + c0;
+        }
+        if (n > F32_LCAP) {
+            // ---- dense block: the CTA-wide coder on the shared-memory block (also raw fallback, CvxCompress.cpp:350-360) ----
+            __syncthreads();
+            if (!in_smem) write_back();
+            __syncthreads();
+            auto get8 = [&](int g, float* c) {
+                const int i = g * 8;
+                float4 a = *reinterpret_cast<const float4*>(&sm[physr(i, 5)]);
+                float4 b = *reinterpret_cast<const float4*>(&sm[physr(i + 4, 5)]);
+                c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+            };
+            encode_tail<F32_T>(p, t, sm, mulfac, get8, [](long i) { return (long)physr((int)i, 5); },
+                               reinterpret_cast<int4*>(s_list), scratch, &s_off);
+            if (tid == 0) {
+                const unsigned int nt = atomicAdd(p.ticket, 1u);
+                s_ticket[(it + 1) & 1] = nt;
+                if (use_tma && nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
+            }
+            __syncthreads();
+            continue;
+        }
+        // ---- sparse block ----
+        __syncthreads();                 // s_base complete; nobody reads the block buffer any more
+        if (tid == 0) {                  // the next block streams in while this one is coded
+            const unsigned int nt = atomicAdd(p.ticket, 1u);
+            s_ticket[(it + 1) & 1] = nt;
+            if (use_tma && nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
+        }
+        {
+            const float T = nz_threshold(mulfac);
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const bool nz = !(fabsf(v[k][r]) <= T);
+                    const unsigned m = __ballot_sync(0xffffffffu, nz);
+                    if (nz) {
+                        const int row = reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k;
+                        s_list[s_base[row] + __popc(m & lt)] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(v[k][r]));
+                    }
+                }
+        }
+        __syncthreads();
+        // ---- tokens per list entry: thread = contiguous chunk of entries ----
+        const int per = (n + F32_T - 1) / F32_T;
+        const int e0 = min(n, tid * per), e1 = min(n, e0 + per);
+        int bytes = 0;
+        {
+            int prev = e0 > 0 ? (int)s_list[e0 - 1].x : -1;
+            for (int e = e0; e < e1; ++e) {
+                const EntryTok k = entry_token(s_list, n, e, prev, mulfac);
+                bytes += k.bytes;
+                prev = (int)s_list[e].x;
+            }
+        }
+        int len;
+        int pos = cta_excl_sum<F32_T>(bytes, scratch, len);
+        const int tail_run = F32_B - 1 - (n > 0 ? (int)s_list[n - 1].x : -1);      // final flush (:294)
+        const int tail_pos = len;
+        len += run_bytes(tail_run);
+        const bool direct = len > F32_STAGE - 8;
+        if (direct) {
+            if (warp == 0) {
+                const unsigned long long excl = place_block(p, t, (unsigned long long)len, false);
+                if (lane == 0) s_off = excl;
+            }
+            __syncthreads();
+        }
+        const bool fits = !direct || (long)(s_off + (unsigned long long)len) <= p.cap;
+        unsigned char* out = direct ? p.payload + s_off : s_stage;
+        if (fits) {
+            auto put = [&](int ps, uint8_t b) { out[ps] = b; };
+            int prev = e0 > 0 ? (int)s_list[e0 - 1].x : -1;
+            for (int e = e0; e < e1; ++e) {
+                const EntryTok k = entry_token(s_list, n, e, prev, mulfac);
+                prev = (int)s_list[e].x;
+                if (k.bytes == 0) continue;
+                pos = put_run(k.run, pos, put);
+                if (k.mode == GM_ELEM) {
+                    pos = put_elem(k.q, k.f, pos, put);
+                } else {
+                    const int w = k.mode == GM_S8 ? 2 : 3;
+                    put(pos++, (uint8_t)(k.mode == GM_S8 ? VLESC2_8x : VLESC3_8x));
+                    for (int i = 0; i < 8; ++i) {
+                        const int q = quantise(__fmul_rn(mulfac, __uint_as_float(s_list[e + i].y)));
+                        put(pos++, (uint8_t)(q & 0xFF)); put(pos++, (uint8_t)((q >> 8) & 0xFF));
+                        if (w == 3) put(pos++, (uint8_t)((q >> 16) & 0xFF));
+                    }
+                }
+            }
+            if (tid == 0) put_run(tail_run, tail_pos, put);
+        } else if (tid == 0) {
+            *p.err = -3;
+        }
+        if (!direct) {
+            if (warp == 0) {
+                const unsigned long long excl = place_block(p, t, (unsigned long long)len, false);
+                if (lane == 0) s_off = excl;
+            }
+            __syncthreads();
+            if ((long)(s_off + (unsigned long long)len) <= p.cap) copy_out(p.payload + s_off, s_stage, len);
+            else if (tid == 0) *p.err = -3;
+        }
+        __syncthreads();
+    }
+}

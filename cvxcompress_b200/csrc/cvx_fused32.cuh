@@ -1,0 +1,241 @@
+// cvx_fused32.cuh -- the 32x32x32-block kernels (BASELINE config 1/3/5: the headline shape).
+//
+// One persistent CTA of 512 threads per SM; a block (128 KiB fp32) lives in shared memory in the
+// TMA SWIZZLE_128B layout (cvx_device.cuh) and moves as follows.
+//
+//   k_encode32:  TMA 3-D box load (OOB zero fill == Copy_To_Block's padding, Block_Copy.cpp:92-115)
+//                -> x lines, y lines in shared memory, z lines in REGISTERS (one thread = one line,
+//                all levels, Wavelet_Transform_Fast.cpp:24-145)
+//                -> the block buffer is free again: the TMA load of the CTA's NEXT block is issued
+//                   and overlaps everything below
+//                -> sparse run-length coder: only the non-zero quantised coefficients (typically a
+//                   few % of the block) are compacted, in raster order, into a list; token sizes,
+//                   zero-run lengths and byte offsets are computed per list entry
+//                   (Run_Length_Encode_Slow.cpp:189-294 semantics, byte-identical)
+//                -> bytes staged in shared memory, block offset by decoupled look-back
+//                   (CvxCompress.cpp:365-390), coalesced copy-out.
+//                Blocks whose non-zero count exceeds the list (dense data, ratio < ~3) fall back to
+//                the dense CTA-wide coder of cvx_codec.cuh on the same shared-memory block.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cvx_wavelet.cuh"
+#include "cvx_rle.cuh"
+#include "cvx_device.cuh"
+#include "cvx_codec.cuh"
+
+namespace cvx {
+
+constexpr int F32_T = 512;                    // threads per CTA
+constexpr int F32_B = 32768;                  // cells per block
+constexpr int F32_ROWS = 1024;                // rows of 32 raster-consecutive cells
+constexpr int F32_LCAP = 6144;                // sparse list capacity (entries of 8 bytes)
+constexpr int F32_STAGE = 32768;              // payload staging bytes
+constexpr int F32_OFF_NZM = F32_B * 4;                        // uint32[1024]  non-zero mask per row
+constexpr int F32_OFF_BASE = F32_OFF_NZM + F32_ROWS * 4;      // int32[1024]   list position of the row's first entry
+constexpr int F32_OFF_LIST = F32_OFF_BASE + F32_ROWS * 4;     // uint2[LCAP]   (raster index, coefficient bits)
+constexpr int F32_OFF_STAGE = F32_OFF_LIST + F32_LCAP * 8;    // bytes
+constexpr int F32_SMEM = F32_OFF_STAGE + F32_STAGE;           // 221184
+
+// ---- mbarrier / TMA (sm_90+ PTX) ---------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// 3-D tiled box load: coordinates in elements, innermost first
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* src, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// ---- line passes on the swizzled 32^3 block: addresses reduced to a base register + immediates ----
+// element (x, y, z) lives at float index  z*1024 + y*32 + (x ^ ((y & 7) << 2))
+
+// x lines: the thread's row is 8 chunks of 16 bytes; logical chunk c sits at physical chunk c ^ (row & 7)
+template <bool EXACT, bool FWD>
+__device__ __forceinline__ void f32_pass_x(float* sm)
+{
+#pragma unroll 1
+    for (int r = threadIdx.x; r < F32_ROWS; r += F32_T) {
+        float4* row = reinterpret_cast<float4*>(sm + r * 32);
+        const int k = r & 7;
+        float v[32];
+        if (FWD) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float4 q = row[c ^ k];
+                v[4 * c] = q.x; v[4 * c + 1] = q.y; v[4 * c + 2] = q.z; v[4 * c + 3] = q.w;
+            }
+            fwd_line<32, EXACT>(v);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                row[c ^ k] = make_float4(v[sub_to_reg<32, EXACT>(4 * c)], v[sub_to_reg<32, EXACT>(4 * c + 1)],
+                                         v[sub_to_reg<32, EXACT>(4 * c + 2)], v[sub_to_reg<32, EXACT>(4 * c + 3)]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float4 q = row[c ^ k];
+                v[sub_to_reg<32, EXACT>(4 * c)] = q.x; v[sub_to_reg<32, EXACT>(4 * c + 1)] = q.y;
+                v[sub_to_reg<32, EXACT>(4 * c + 2)] = q.z; v[sub_to_reg<32, EXACT>(4 * c + 3)] = q.w;
+            }
+            inv_line<32, EXACT>(v);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) row[c ^ k] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+        }
+    }
+}
+
+// y lines: thread (x = lane, z); element j at z*1024 + j*32 + (x ^ ((j & 7) << 2)): eight base
+// pointers (one per j & 7) + immediate offsets
+template <bool EXACT, bool FWD>
+__device__ __forceinline__ void f32_pass_y(float* sm)
+{
+#pragma unroll 1
+    for (int l = threadIdx.x; l < F32_ROWS; l += F32_T) {
+        const int x = l & 31, z = l >> 5;
+        float* a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = sm + z * 1024 + (x ^ (k << 2));
+        float v[32];
+        if (FWD) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = a[j & 7][j * 32];
+            fwd_line<32, EXACT>(v);
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { const int s = reg_to_sub<32, EXACT>(r); a[s & 7][s * 32] = v[r]; }
+        } else {
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { const int s = reg_to_sub<32, EXACT>(r); v[r] = a[s & 7][s * 32]; }
+            inv_line<32, EXACT>(v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) a[j & 7][j * 32] = v[j];
+        }
+    }
+}
+
+// z line of thread-line l (x = l & 31, y = l >> 5): element j at j*1024 + y*32 + (x ^ ((y & 7) << 2))
+__device__ __forceinline__ float* f32_zline(float* sm, int l)
+{
+    const int x = l & 31, y = l >> 5;
+    return sm + y * 32 + (x ^ ((y & 7) << 2));
+}
+
+
+// ---- sparse coder pieces ---------------------------------------------------------------------------
+// largest T >= 0 with |fl(m * T)| < 1, so that  quantise(fl(m * v)) != 0  <=>  !(|v| <= T)
+// (truncation gives 0 exactly when |f| < 1; NaN and out-of-range give 0x80000000, Run_Length_Encode_Slow.cpp:204).
+// fl() is monotone, so one threshold decides.  Requires 1e-30 < |m| < 1e30.
+__device__ __forceinline__ float nz_threshold(float m)
+{
+    const float am = fabsf(m);
+    float t = __fdiv_rn(1.0f, am);
+    for (int i = 0; i < 8 && !(__fmul_rn(am, t) < 1.0f); ++i) t = __uint_as_float(__float_as_uint(t) - 1u);
+    for (int i = 0; i < 8; ++i) {
+        const float u = __uint_as_float(__float_as_uint(t) + 1u);
+        if (__fmul_rn(am, u) < 1.0f) t = u; else break;
+    }
+    return t;
+}
+
+// One entry of the sorted non-zero list.  Returns the bytes it emits (its zero-run flush included) and, through
+// `mode`/`lead`, whether it belongs to an aligned group of 8 non-zeros coded as one VLESC2_8x / VLESC3_8x token
+// (Run_Length_Encode_Slow.cpp:231-256); such a group is written by its first entry alone.
+struct EntryTok {
+    int run;        // zeros between the previous non-zero and this one
+    int q;          // quantised value
+    float f;        // scaled value (VLESC4 payload)
+    int mode;       // GM_ELEM, GM_S8, GM_T8
+    int bytes;      // bytes this entry is responsible for
+};
+__device__ __forceinline__ EntryTok entry_token(const uint2* list, int n, int e, int prev_idx, float mulfac)
+{
+    EntryTok k;
+    const uint2 ent = list[e];
+    const int idx = (int)ent.x;
+    k.run = idx - prev_idx - 1;
+    k.f = __fmul_rn(mulfac, __uint_as_float(ent.y));
+    k.q = quantise(k.f);
+    k.mode = GM_ELEM;
+    const int j = idx & 7, le = e - j;
+    if (le >= 0 && le + 7 < n && (int)list[le].x == idx - j && (int)list[le + 7].x == idx - j + 7) {
+        int q8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q8[i] = quantise(__fmul_rn(mulfac, __uint_as_float(list[le + i].y)));
+        k.mode = group_mode(q8);
+    }
+    if (k.mode == GM_ELEM) k.bytes = run_bytes(k.run) + elem_bytes(k.q);
+    else k.bytes = j == 0 ? run_bytes(k.run) + (k.mode == GM_S8 ? 17 : 25) : 0;
+    return k;
+}
+
+template <class Put>
+__device__ __forceinline__ int put_elem(int v, float f, int pos, Put put)
+{
+    if (is_b(v)) { put(pos, (uint8_t)(v & 0xFF)); return pos + 1; }
+    if (is_s(v)) { put(pos, (uint8_t)VLESC2); put(pos + 1, (uint8_t)(v & 0xFF)); put(pos + 2, (uint8_t)((v >> 8) & 0xFF)); return pos + 3; }
+    if (is_3(v)) {
+        put(pos, (uint8_t)VLESC3); put(pos + 1, (uint8_t)(v & 0xFF)); put(pos + 2, (uint8_t)((v >> 8) & 0xFF));
+        put(pos + 3, (uint8_t)((v >> 16) & 0xFF));
+        return pos + 4;
+    }
+    const uint32_t u = __float_as_uint(f);      // VLESC4 carries the SCALED float (:267-270)
+    put(pos, (uint8_t)VLESC4); put(pos + 1, (uint8_t)(u & 0xFF)); put(pos + 2, (uint8_t)((u >> 8) & 0xFF));
+    put(pos + 3, (uint8_t)((u >> 16) & 0xFF)); put(pos + 4, (uint8_t)(u >> 24));
+    return pos + 5;
+}
+
+// staged payload (shared memory, 16-byte aligned) -> global, any destination alignment: 32-bit coalesced stores
+__device__ __forceinline__ void copy_out(unsigned char* dst, const unsigned char* stage, int len)
+{
+    const int tid = threadIdx.x;
+    int head = (int)((4u - (unsigned)(reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u);
+    if (head > len) head = len;
+    if (tid < head) dst[tid] = stage[tid];
+    const int nw = (len - head) >> 2;
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(stage);
+    for (int k = tid; k < nw; k += F32_T) {
+        const uint32_t lo = s32[k];
+        d32[k] = head ? __funnelshift_r(lo, s32[k + 1], 8 * head) : lo;
+    }
+    const int done = head + 4 * nw;
+    if (tid < len - done) dst[done + tid] = stage[done + tid];
+}
+
+}  // namespace cvx

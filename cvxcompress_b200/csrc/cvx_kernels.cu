@@ -15,11 +15,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <string.h>
 #include "cvx_wavelet.cuh"
 #include "cvx_rle.cuh"
 #include "cvx_device.cuh"
 #include "cvx_codec.cuh"
+#include "cvx_fused32.cuh"
 #include "cvx_internal.h"
+#include <cudaTypedefs.h>
 
 namespace cvx {
 
@@ -444,6 +447,8 @@ __global__ void __launch_bounds__(T, MINB) k_encode_fused(const EncParams p)
     }
 }
 
+#include "cvx_encode32.inl"
+
 // ------------------------------------------------------------------------------------------
 // Fused decode
 // ------------------------------------------------------------------------------------------
@@ -699,6 +704,37 @@ static VolView vol_view(const Shape& s, const void* vol)
     return g;
 }
 
+// 3-D tiled tensor map over an nx-fastest fp32 volume, box bx x by x bz, SWIZZLE_128B (the block layout of
+// cvx_device.cuh), out-of-bounds cells read as zero (== Copy_To_Block's padding, Block_Copy.cpp:92-115).
+// Returns false when TMA cannot address the volume (base not 16-byte aligned or nx % 4 != 0): the kernels then
+// take their plain-load path.
+bool make_volume_tmap(CUtensorMap* map, const void* d_vol, int nx, int ny, int nz, int bx, int by, int bz)
+{
+    memset(map, 0, sizeof(*map));
+    if ((reinterpret_cast<uintptr_t>(d_vol) & 15) != 0 || (nx & 3) != 0 || bx * 4 > 128) return false;
+    static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+        else
+            cudaGetLastError();
+    }
+    if (!encode) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz};
+    const cuuint64_t strides[2] = {(cuuint64_t)nx * 4, (cuuint64_t)nx * (cuuint64_t)ny * 4};
+    const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, (cuuint32_t)bz};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(d_vol), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
 cudaError_t ws_reserve_status(cvxgpu_workspace* ws, long nblk)
 {
     if (nblk <= ws->status_cap) return cudaSuccess;
@@ -804,6 +840,17 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
     p.payload = reinterpret_cast<uint8_t*>(d_payload); p.cap = cap; p.status = ws->d_status; p.ticket = ws->d_ticket;
     p.payload_bytes = d_payload_bytes; p.err = d_err;
     rle_segments(p.s, p.nseg, p.gps);
+    if (s.bx == 32 && s.by == 32 && s.bz == 32) {
+        // the headline shape: TMA-fed persistent kernel with the sparse coder (cvx_fused32.cuh)
+        CUtensorMap tmap;
+        const int use_tma = make_volume_tmap(&tmap, d_vol, s.nx, s.ny, s.nz, 32, 32, 8) ? 1 : 0;
+        auto kern = exact ? k_encode32<true> : k_encode32<false>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F32_SMEM);
+        if (e != cudaSuccess) return e;
+        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
+        kern<<<(unsigned)grid, F32_T, F32_SMEM, st>>>(tmap, p, use_tma);
+        return cudaGetLastError();
+    }
     if (fused_ok(s.bx, s.by, s.bz)) {
         const size_t smem = (size_t)p.s.B * 4 + sizeof(int4) * (size_t)p.nseg;
 #define CVX_CALL_ENC(MAXN, EX, T, MINB) \
