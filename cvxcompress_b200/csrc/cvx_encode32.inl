@@ -1,13 +1,52 @@
 // cvx_encode32.inl -- k_encode32, included by cvx_kernels.cu inside namespace cvx after EncParams,
 // gather_block, cta_sumsq*, encode_tail (design notes: cvx_fused32.cuh).
 
-// publish this block's byte count in ticket order, fill its table entry, return its payload offset (warp 0, all lanes)
-__device__ __forceinline__ unsigned long long place_block(const EncParams& p, long t, unsigned long long nbytes, bool raw)
+// ---- placing block payloads in natural (ticket) order without stalling the pipeline -------------------------
+// A block's byte count is published as an AGGREGATE the moment it is known; its exclusive prefix (= payload
+// offset) is only needed for the copy-out, which is deferred by one block: by then every ticket in flight next
+// to it has published, so the look-back below finds its words ready instead of spinning on the slowest CTA of the
+// wave (measured: 30 % of the kernel waited in the undeferred version).  The look-back reads F32_T status words
+// per round with the whole CTA (one L2 round trip for a window deeper than the grid).
+__device__ __forceinline__ void publish_aggregate(const EncParams& p, long t, unsigned long long len)
 {
-    const unsigned long long excl = lookback_exclusive(p.status, t, nbytes);
-    if (lane_id() == 0) {
-        p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);              // CvxCompress.cpp:382-384
-        if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + nbytes);
+    st_release_u64(&p.status[t], (t == 0 ? CVX_ST_PFX : CVX_ST_AGG) | len);
+}
+
+// all F32_T threads; returns the exclusive prefix of ticket t to every thread.  scratch64: >= 18 words.
+__device__ __forceinline__ unsigned long long wide_lookback(const EncParams& p, long t, unsigned long long len, bool raw,
+                                                            unsigned long long* scratch64)
+{
+    unsigned long long excl = 0;
+    if (t > 0) {
+        long j = t - 1;
+        for (;;) {
+            const long idx = j - threadIdx.x;
+            unsigned long long s = CVX_ST_PFX;                      // before ticket 0: prefix 0
+            if (idx >= 0) {
+                do { s = ld_acquire_u64(&p.status[idx]); } while ((s >> 62) == 0);
+            }
+            const unsigned pfx = __ballot_sync(0xffffffffu, (s >> 62) == 2);
+            const int first = pfx ? __ffs(pfx) - 1 : 32;            // nearest predecessor in this warp holding a prefix
+            unsigned long long v = (lane_id() <= first) ? (s & CVX_ST_MASK) : 0ull;
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+            if (lane_id() == 0) scratch64[warp_id()] = v | (pfx ? (1ull << 63) : 0ull);
+            __syncthreads();
+            bool done = false;
+            for (int w = 0; w < F32_T / 32; ++w) {                  // warps in look-back order; stop at the first prefix
+                const unsigned long long x = scratch64[w];
+                excl += x & ~(1ull << 63);
+                if (x >> 63) { done = true; break; }
+            }
+            __syncthreads();
+            if (done) break;
+            j -= F32_T;
+        }
+        if (threadIdx.x == 0) st_release_u64(&p.status[t], CVX_ST_PFX | (excl + len));
+    }
+    if (threadIdx.x == 0) {
+        p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);      // CvxCompress.cpp:382-384
+        if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + len);
     }
     return excl;
 }
@@ -26,6 +65,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     __shared__ float s_red[32];
     __shared__ unsigned int s_ticket[2];
     __shared__ unsigned long long s_off;
+    __shared__ unsigned long long s_lb[F32_T / 32 + 2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -48,6 +88,17 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         if (use_tma && t0 < p.nblk) { fence_proxy_async(); issue_load(t0); }
     }
     __syncthreads();
+
+    // the block whose payload sits in a staging buffer awaiting its offset (deferred copy-out)
+    long pend_t = -1;
+    int pend_len = 0, buf = 0;
+    auto complete_pending = [&]() {
+        if (pend_t < 0) return;
+        const unsigned long long excl = wide_lookback(p, pend_t, (unsigned long long)pend_len, false, s_lb);
+        if ((long)(excl + (unsigned long long)pend_len) <= p.cap) copy_out(p.payload + excl, s_stage + (buf ^ 1) * F32_STAGE, pend_len);
+        else if (tid == 0) *p.err = -3;
+        pend_t = -1;
+    };
 
     uint32_t parity = 0;
     for (int it = 0;; ++it) {
@@ -174,16 +225,12 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         const int tail_run = F32_B - 1 - (n > 0 ? (int)s_list[n - 1].x : -1);      // final flush (:294)
         const int tail_pos = len;
         len += run_bytes(tail_run);
+        if (tid == 0) publish_aggregate(p, t, (unsigned long long)len);
         const bool direct = len > F32_STAGE - 8;
-        if (direct) {
-            if (warp == 0) {
-                const unsigned long long excl = place_block(p, t, (unsigned long long)len, false);
-                if (lane == 0) s_off = excl;
-            }
-            __syncthreads();
-        }
-        const bool fits = !direct || (long)(s_off + (unsigned long long)len) <= p.cap;
-        unsigned char* out = direct ? p.payload + s_off : s_stage;
+        unsigned long long excl_now = 0;
+        if (direct) excl_now = wide_lookback(p, t, (unsigned long long)len, false, s_lb);     // rare: ratio < ~5
+        const bool fits = !direct || (long)(excl_now + (unsigned long long)len) <= p.cap;
+        unsigned char* out = direct ? p.payload + excl_now : s_stage + buf * F32_STAGE;
         if (fits) {
             auto put = [&](int ps, uint8_t b) { out[ps] = b; };
             int prev = e0 > 0 ? (int)s_list[e0 - 1].x : -1;
@@ -208,15 +255,11 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         } else if (tid == 0) {
             *p.err = -3;
         }
-        if (!direct) {
-            if (warp == 0) {
-                const unsigned long long excl = place_block(p, t, (unsigned long long)len, false);
-                if (lane == 0) s_off = excl;
-            }
-            __syncthreads();
-            if ((long)(s_off + (unsigned long long)len) <= p.cap) copy_out(p.payload + s_off, s_stage, len);
-            else if (tid == 0) *p.err = -3;
-        }
+        // the PREVIOUS staged block gets its offset now (its neighbours published a block time ago) and is copied out
+        complete_pending();
+        if (!direct) { pend_t = t; pend_len = len; buf ^= 1; }
         __syncthreads();
     }
+    __syncthreads();
+    complete_pending();
 }

@@ -30,13 +30,13 @@ namespace cvx {
 constexpr int F32_T = 512;                    // threads per CTA
 constexpr int F32_B = 32768;                  // cells per block
 constexpr int F32_ROWS = 1024;                // rows of 32 raster-consecutive cells
-constexpr int F32_LCAP = 6144;                // sparse list capacity (entries of 8 bytes)
-constexpr int F32_STAGE = 32768;              // payload staging bytes
+constexpr int F32_LCAP = 4096;                // sparse list capacity (entries of 8 bytes): 12.5 % non-zeros
+constexpr int F32_STAGE = 24576;              // payload staging bytes, two buffers (deferred copy-out)
 constexpr int F32_OFF_NZM = F32_B * 4;                        // uint32[1024]  non-zero mask per row
 constexpr int F32_OFF_BASE = F32_OFF_NZM + F32_ROWS * 4;      // int32[1024]   list position of the row's first entry
 constexpr int F32_OFF_LIST = F32_OFF_BASE + F32_ROWS * 4;     // uint2[LCAP]   (raster index, coefficient bits)
 constexpr int F32_OFF_STAGE = F32_OFF_LIST + F32_LCAP * 8;    // bytes
-constexpr int F32_SMEM = F32_OFF_STAGE + F32_STAGE;           // 221184
+constexpr int F32_SMEM = F32_OFF_STAGE + 2 * F32_STAGE;       // 221184
 
 // ---- mbarrier / TMA (sm_90+ PTX) ---------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
