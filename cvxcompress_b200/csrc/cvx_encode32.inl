@@ -51,6 +51,18 @@ __device__ __forceinline__ unsigned long long wide_lookback(const EncParams& p, 
     return excl;
 }
 
+// optional per-phase cycle accounting (make TIMING=1): thread 0 stamps clock64() at phase boundaries
+#ifdef CVX_PHASE_TIMING
+__device__ unsigned long long g_phase[2][16];
+#define CVX_PH_DECL long long ph_last = clock64(); unsigned long long ph_acc[12] = {0}
+#define CVX_PH(i) do { if (threadIdx.x == 0) { long long c_ = clock64(); ph_acc[i] += (unsigned long long)(c_ - ph_last); ph_last = c_; } } while (0)
+#define CVX_PH_FLUSH(k) do { if (threadIdx.x == 0) for (int i_ = 0; i_ < 12; ++i_) atomicAdd(&g_phase[k][i_], ph_acc[i_]); } while (0)
+#else
+#define CVX_PH_DECL
+#define CVX_PH(i)
+#define CVX_PH_FLUSH(k)
+#endif
+
 template <bool EXACT>
 __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ CUtensorMap tmap, const EncParams p, const int use_tma)
 {
@@ -101,12 +113,14 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     };
 
     uint32_t parity = 0;
+    CVX_PH_DECL;
     for (int it = 0;; ++it) {
         const long t = s_ticket[it & 1];
         if (t >= p.nblk) break;
         if (use_tma) {
             mbar_wait(&s_bar, parity);
             parity ^= 1u;
+            CVX_PH(0);
         } else {
             const int iix = (int)(t % p.nbx);
             const long q = t / p.nbx;
@@ -115,8 +129,10 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         }
         f32_pass_x<EXACT, true>(sm);
         __syncthreads();
+        CVX_PH(1);
         f32_pass_y<EXACT, true>(sm);
         __syncthreads();
+        CVX_PH(2);
         // z lines stay in registers: thread-line l = tid + 512 k is (x = lane, y = warp + 16 k)
         float v[2][32];
 #pragma unroll
@@ -160,6 +176,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
                     if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
                 }
             __syncthreads();
+            CVX_PH(3);
             const int c0 = __popc(s_nzm[2 * tid]), c1 = __popc(s_nzm[2 * tid + 1]);
             const int base = cta_excl_sum<F32_T>(c0 + c1, scratch, n);
             s_base[2 * tid] = base;
@@ -188,6 +205,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         }
         // ---- sparse block ----
         __syncthreads();                 // s_base complete; nobody reads the block buffer any more
+        CVX_PH(4);
         if (tid == 0) {                  // the next block streams in while this one is coded
             const unsigned int nt = atomicAdd(p.ticket, 1u);
             s_ticket[(it + 1) & 1] = nt;
@@ -201,13 +219,15 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
                 for (int r = 0; r < 32; ++r) {
                     const bool nz = !(fabsf(v[k][r]) <= T);
                     const unsigned m = __ballot_sync(0xffffffffu, nz);
-                    if (nz) {
-                        const int row = reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k;
-                        s_list[s_base[row] + __popc(m & lt)] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(v[k][r]));
-                    }
+                    // unconditional (broadcast) load of the row base: 64 independent loads pipeline instead of
+                    // 64 dependent load->store chains inside divergent branches
+                    const int row = reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k;
+                    const int at = s_base[row] + __popc(m & lt);
+                    if (nz) s_list[at] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(v[k][r]));
                 }
         }
         __syncthreads();
+        CVX_PH(5);
         // ---- tokens per list entry: thread = contiguous chunk of entries ----
         const int per = (n + F32_T - 1) / F32_T;
         const int e0 = min(n, tid * per), e1 = min(n, e0 + per);
@@ -222,6 +242,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         }
         int len;
         int pos = cta_excl_sum<F32_T>(bytes, scratch, len);
+        CVX_PH(6);
         const int tail_run = F32_B - 1 - (n > 0 ? (int)s_list[n - 1].x : -1);      // final flush (:294)
         const int tail_pos = len;
         len += run_bytes(tail_run);
@@ -256,10 +277,14 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             *p.err = -3;
         }
         // the PREVIOUS staged block gets its offset now (its neighbours published a block time ago) and is copied out
+        CVX_PH(7);
         complete_pending();
+        CVX_PH(8);
         if (!direct) { pend_t = t; pend_len = len; buf ^= 1; }
         __syncthreads();
+        CVX_PH(9);
     }
     __syncthreads();
     complete_pending();
+    CVX_PH_FLUSH(0);
 }

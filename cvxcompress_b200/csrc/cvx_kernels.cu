@@ -973,3 +973,19 @@ cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, 
 }
 
 }  // namespace cvx
+
+// developer aid (make TIMING=1): per-phase cycle totals stamped by thread 0 of every CTA; kind 0 = encode, 1 = decode
+extern "C" int cvx_debug_phases(unsigned long long* out, int kind, int reset)
+{
+#ifdef CVX_PHASE_TIMING
+    unsigned long long h[2][16];
+    if (cudaMemcpyFromSymbol(h, cvx::g_phase, sizeof(h)) != cudaSuccess) return -1;
+    for (int i = 0; i < 16; ++i) out[i] = h[kind & 1][i];
+    if (reset) { memset(h, 0, sizeof(h)); cudaMemcpyToSymbol(cvx::g_phase, h, sizeof(h)); }
+    return 16;
+#else
+    (void)out; (void)kind; (void)reset;
+    return 0;
+#endif
+}
+
