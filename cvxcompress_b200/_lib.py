@@ -9,7 +9,8 @@ import os
 import subprocess
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "lib", "libcvxcompress.so")
+# CVXCOMPRESS_LIB: developer override (e.g. the `make TIMING=1 OUT=../lib_timing` build)
+LIB_PATH = os.environ.get("CVXCOMPRESS_LIB") or os.path.join(PKG_DIR, "lib", "libcvxcompress.so")
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 
 OK, ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STREAM = 0, -1, -2, -3, -4
