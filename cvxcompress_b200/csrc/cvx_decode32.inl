@@ -1,0 +1,250 @@
+// cvx_decode32.inl -- k_decode32, included by cvx_kernels.cu inside namespace cvx after DecParams.
+//
+// One persistent CTA of 512 threads per SM; per 32^3 block:
+//   payload window (8 KiB, cp.async-prefetched while the PREVIOUS block is transformed)
+//   -> speculative token parse over 8-byte chunks, two chunks per thread (Run_Length_Decode_Slow,
+//      Run_Length_Encode_Slow.cpp:388-527): walk, verify/repair the chain, count, scan, expand into the
+//      pre-zeroed shared-memory block (TMA SWIZZLE_128B layout, cvx_device.cuh)
+//   -> inverse x lines, inverse y lines in shared memory (Wavelet_Transform_Fast.cpp:148-279 order)
+//   -> inverse z lines in REGISTERS; the block buffer is zeroed for the next block at once and the
+//      results go straight to the volume as 128-byte row stores (Copy_From_Block clipping,
+//      Block_Copy.cpp:136-212) -- no write-back to shared memory, no alignment requirement on the volume.
+// A block's payload length is not stored in the stream; when the next table entry is larger (natural block
+// order) the difference bounds the first window, otherwise the full window is parsed.  Either way parsing
+// continues window by window until 32768 values exist, so any block order decodes.
+
+constexpr int D32_T = 512;
+constexpr int D32_CH = 1024;                          // 8-byte chunks per window, two per thread
+constexpr int D32_WIN = D32_CH * 8 + 32;              // + look-ahead for tokens straddling the window end
+constexpr int D32_OFF_WIN = F32_B * 4;                // two windows
+constexpr int D32_OFF_EXT = D32_OFF_WIN + 2 * D32_WIN;
+constexpr int D32_SMEM = D32_OFF_EXT + D32_CH * 4;    // 151 648 bytes
+
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, int src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// stage the window [cbase, cbase + D32_WIN) (cbase 16-byte aligned); bytes at or beyond `hi` read as zero
+__device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi)
+{
+    for (int g = threadIdx.x; g < D32_WIN / 16; g += D32_T) {
+        const uint8_t* a = cbase + 16 * g;
+        long left = hi - a;
+        int n = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
+        cp_async16_zfill(win + 16 * g, n > 0 ? a : cbase, n);
+    }
+    cp_async_commit();
+}
+
+// exclusive sum of a pair of 32-bit counts packed in 64 bits (each count <= 2^20, 512 threads: no carry between halves)
+__device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long v, unsigned long long* scratch64, unsigned long long& total)
+{
+    unsigned long long x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane_id() >= d) x += y;
+    }
+    if (lane_id() == 31) scratch64[warp_id()] = x;
+    __syncthreads();
+    unsigned long long w = lane_id() < D32_T / 32 ? scratch64[lane_id()] : 0ull;
+    unsigned long long s = w;
+#pragma unroll
+    for (int d = 1; d < 16; d <<= 1) {
+        unsigned long long y = __shfl_up_sync(0xffffffffu, s, d);
+        if (lane_id() >= d) s += y;
+    }
+    total = __shfl_sync(0xffffffffu, s, D32_T / 32 - 1);
+    const unsigned long long wbase = __shfl_sync(0xffffffffu, s - w, warp_id());
+    __syncthreads();
+    return wbase + x - v;
+}
+
+struct D32Src {
+    const uint8_t* src;     // first payload byte of the block
+    long hint;              // payload bytes of the block when the table tells, else 0
+    int raw;
+    float scalefac;
+};
+
+// table entry of block t -> where its payload is (CvxCompress.cpp:545-548) and, when the next entry is larger, how long
+__device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
+{
+    D32Src r;
+    unsigned long long o = p.offs[t];
+    r.raw = (int)(o >> 63);
+    o &= 0x7FFFFFFFFFFFFFFFull;
+    r.src = p.payload + o;
+    long nxt = (t + 1 < p.nblk) ? (long)(p.offs[t + 1] & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
+    long h = nxt - (long)o;
+    r.hint = (h > 0 && h <= 5L * F32_B + 8) ? h : 0;
+    const float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
+    r.scalefac = __fdiv_rn(1.0f, mulfac);                        // Run_Length_Encode_Slow.cpp:392
+    return r;
+}
+
+// parse the block whose first window is already staged in `win`; writes coefficients through put(i, v)
+template <class PutV>
+__device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, unsigned char* win, int* s_ext,
+                                          unsigned long long* scratch64, PutV put)
+{
+    const int tid = threadIdx.x;
+    const uint8_t* cbase = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(b.src) & ~(uintptr_t)15);
+    int entry = (int)(b.src - cbase);
+    long hint = b.hint;
+    int produced = 0;
+    const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
+    auto getb = [&](int k) -> uint32_t { return (uint32_t)win[k]; };
+    for (bool first = true;; first = false) {
+        if (!first) {                     // rare: payload longer than one window, or a wrong hint
+            __syncthreads();
+            d32_issue_window(win, cbase, hi);
+            cp_async_wait_all();
+            __syncthreads();
+        }
+        int nch = D32_CH;
+        if (hint > 0) {
+            long want = (entry + hint + 7) >> 3;
+            want += want & 1;             // even: the next window base stays 16-byte aligned
+            if (want < nch) nch = (int)want;
+        }
+        uint64_t A[2], N[2];
+        uint32_t mask[2];
+        int ent[2], ext[2], cnt[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int c = tid + D32_T * j;
+            mask[j] = 0; ent[j] = 0; ext[j] = 0; cnt[j] = 0; A[j] = 0; N[j] = 0;
+            if (c < nch) {
+                A[j] = w64[c]; N[j] = w64[c + 1];
+                int d, dummy = 0;
+                if (c == 0) d = entry;
+                else if (c == 1) { d = entry; chunk8_walk<false>(w64[0], 0ull, d, dummy); }
+                else { d = 0; chunk8_walk<false>(w64[c - 2], 0ull, d, dummy); chunk8_walk<false>(w64[c - 1], 0ull, d, dummy); }
+                ent[j] = d;
+                mask[j] = chunk8_walk<true>(A[j], N[j], d, cnt[j]);
+                ext[j] = d;
+            }
+        }
+        for (;;) {                        // verify exit(c-1) == entry(c); repair until the chain is consistent
+#pragma unroll
+            for (int j = 0; j < 2; ++j) { const int c = tid + D32_T * j; if (c < nch) s_ext[c] = ext[j]; }
+            __syncthreads();
+            bool bad[2];
+            int want[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int c = tid + D32_T * j;
+                want[j] = (c > 0 && c < nch) ? s_ext[c - 1] : ent[j];
+                bad[j] = want[j] != ent[j];
+            }
+            const int last_ext = s_ext[nch - 1];
+            const int any = __syncthreads_or((bad[0] || bad[1]) ? 1 : 0);
+            if (!any) { entry = last_ext; break; }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                if (bad[j]) { int d = want[j]; ent[j] = d; cnt[j] = 0; mask[j] = chunk8_walk<true>(A[j], N[j], d, cnt[j]); ext[j] = d; }
+        }
+        const unsigned c0 = (unsigned)min(cnt[0], 1 << 20), c1 = (unsigned)min(cnt[1], 1 << 20);
+        unsigned long long total;
+        const unsigned long long ex = d32_excl_sum64((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
+        const long tot0 = (long)(total & 0xFFFFFFFFull), tot1 = (long)(total >> 32);
+        long vi0 = (long)produced + (long)(ex & 0xFFFFFFFFull);
+        long vi1 = (long)produced + tot0 + (long)(ex >> 32);
+        if (mask[0] && vi0 < F32_B) chunk8_expand(mask[0], A[0], N[0], 8 * tid, (int)vi0, F32_B, b.scalefac, getb, put);
+        if (mask[1] && vi1 < F32_B) chunk8_expand(mask[1], A[1], N[1], 8 * (tid + D32_T), (int)vi1, F32_B, b.scalefac, getb, put);
+        long np = (long)produced + tot0 + tot1;
+        produced = np > (1 << 30) ? (1 << 30) : (int)np;
+        if (produced >= F32_B) break;
+        cbase += 8 * nch;
+        hint = 0;
+        if (cbase >= hi + 64) break;      // truncated stream: stop instead of spinning
+    }
+}
+
+template <bool EXACT>
+__global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    unsigned char* s_win = smem_raw + D32_OFF_WIN;
+    int* s_ext = reinterpret_cast<int*>(smem_raw + D32_OFF_EXT);
+    __shared__ unsigned long long scratch64[D32_T / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint8_t* hi = p.payload + p.payload_bytes;
+    const long plane = (long)p.g.nx * p.g.ny;
+
+    long t = blockIdx.x;
+    if (t >= p.nblk) return;
+    D32Src cur = d32_locate(p, t);
+    int buf = 0;
+    d32_issue_window(s_win, reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(cur.src) & ~(uintptr_t)15), hi);
+    {
+        float4* z4 = reinterpret_cast<float4*>(sm);
+#pragma unroll
+        for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (;;) {
+        const long tn = t + gridDim.x;
+        D32Src nxt = cur;
+        if (tn < p.nblk) nxt = d32_locate(p, tn);                   // table reads overlap the parse below
+        cp_async_wait_all();
+        __syncthreads();                                            // window staged, block buffer zeroed
+        if (cur.raw) {                                              // CvxCompress.cpp:555: B fp32 coefficients
+            for (int i = tid; i < F32_B; i += D32_T) {
+                uint32_t u = 0;
+                const uint8_t* s = cur.src + 4L * i;
+                if ((reinterpret_cast<uintptr_t>(cur.src) & 3) == 0 && s + 4 <= hi) u = *reinterpret_cast<const uint32_t*>(s);
+                else for (int k = 0; k < 4; ++k) if (s + k < hi) u |= (uint32_t)s[k] << (8 * k);
+                sm[physr(i, 5)] = __uint_as_float(u);
+            }
+        } else {
+            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, [&](int i, float v) { sm[physr(i, 5)] = v; });
+        }
+        __syncthreads();
+        if (tn < p.nblk)                                            // next block's payload streams in under the transform
+            d32_issue_window(s_win + (buf ^ 1) * D32_WIN,
+                             reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi);
+        f32_pass_x<EXACT, false>(sm);
+        __syncthreads();
+        f32_pass_y<EXACT, false>(sm);
+        __syncthreads();
+        float v[2][32];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float* zl = f32_zline(sm, tid + D32_T * k);
+#pragma unroll
+            for (int r = 0; r < 32; ++r) v[k][r] = zl[reg_to_sub<32, EXACT>(r) * 1024];
+        }
+        __syncthreads();                                            // every z line is in registers
+        {
+            float4* z4 = reinterpret_cast<float4*>(sm);
+#pragma unroll
+            for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        const int gx = iix * 32 + lane, gz0 = iiz * 32;
+        const int nzl = min(32, p.g.nz - gz0);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            inv_line<32, EXACT>(v[k]);
+            const int gy = iiy * 32 + warp + 16 * k;
+            if (gx < p.g.nx && gy < p.g.ny) {
+                float* dst = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < nzl) dst[j * plane] = v[k][j];
+            }
+        }
+        if (tn >= p.nblk) break;
+        t = tn;
+        cur = nxt;
+        buf ^= 1;
+    }
+}

@@ -523,6 +523,8 @@ __global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams p)
     }
 }
 
+#include "cvx_decode32.inl"
+
 // forward / inverse transform of dense blocks: block k is the z-range [k*bz, (k+1)*bz) of a
 // bx * by * (bz*nblocks) volume
 template <int MAXN, bool EXACT, bool FWD, int T, int MINB>
@@ -897,6 +899,15 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
     p.glob_mulfac = glob_mulfac; p.use_local = use_local; p.offs = d_offs; p.blkmulfac = d_blkmulfac;
     p.payload = reinterpret_cast<const uint8_t*>(d_payload); p.payload_bytes = payload_bytes;
     cudaError_t e = cudaSuccess;
+    if (s.bx == 32 && s.by == 32 && s.bz == 32) {
+        // the headline shape: prefetched payload windows, z lines in registers, direct row stores (cvx_decode32.inl)
+        auto kern = exact ? k_decode32<true> : k_decode32<false>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, D32_SMEM);
+        if (e != cudaSuccess) return e;
+        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
+        kern<<<(unsigned)grid, D32_T, D32_SMEM, st>>>(p);
+        return cudaGetLastError();
+    }
     if (fused_ok(s.bx, s.by, s.bz)) {
 #define CVX_CALL_DEC(MAXN, EX, T, MINB)                                                   \
     do {                                                                                  \

@@ -22,6 +22,7 @@
 #pragma once
 #include <stdint.h>
 #include <limits.h>
+#include <string.h>
 #include "cvx_wavelet.cuh"
 
 namespace cvx {
@@ -291,6 +292,91 @@ CVX_HD void chunk_expand(uint32_t mask, const uint32_t w[4], int base, int vi, i
             }
             vi += 8;
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// 8-byte chunk decoder pieces (k_decode32).  A = the chunk's 8 payload bytes (little endian),
+// N = the 8 bytes that follow it (operands of tokens that start near the chunk's end).  Every byte
+// position is a compile-time constant after unrolling, so operand extraction is a static shift.
+// ------------------------------------------------------------------------------------------
+// low 32 bits of the 128-bit value (N:A) >> 8*(p+1): the up-to-4 operand bytes of a token starting at byte p
+CVX_HD uint32_t chunk8_operand(uint64_t A, uint64_t N, int p)
+{
+    const int s = 8 * (p + 1);
+    if (s >= 64) return (uint32_t)N;
+    uint64_t x = A >> s;
+    if (s > 32) x |= N << (64 - s);
+    return (uint32_t)x;
+}
+
+// Walk one chunk: d = bytes until the next token start on entry and on return; bit p of the result marks a
+// token start at byte p.  COUNT: n += number of values produced by the tokens that start in this chunk.
+template <bool COUNT>
+CVX_HD uint32_t chunk8_walk(uint64_t A, uint64_t N, int& d, int& n)
+{
+    uint32_t mask = 0;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const uint32_t b = (uint32_t)(A >> (8 * p)) & 0xFFu;
+        const int L = token_len(b);
+        const bool st = (d == 0);
+        mask |= (st ? 1u : 0u) << p;
+        if (COUNT) {
+            const uint32_t op = chunk8_operand(A, N, p);
+            int c = 1;
+            c = (b == 0x7Fu) ? (int)(op & 0xFFu) : c;                 // RLESC1
+            c = (b == 0x7Du) ? (int)(op & 0xFFFFFFu) : c;             // RLESC3
+            c = (b == 0x7Eu || b == 0x82u) ? 8 : c;                   // VLESC3_8x, VLESC2_8x
+            n += st ? c : 0;
+        }
+        d = st ? L : d;
+        d -= 1;
+    }
+    return mask;
+}
+
+// Write the values of the tokens that start in this chunk (Run_Length_Encode_Slow.cpp:415-513).  vi = raster index
+// of the first value; zeros are not written (pre-zeroed destination).  getb(k) = byte k of the staged window,
+// base = window index of this chunk's first byte (used by the rare 17/25-byte tokens only).
+template <class GetB, class PutV>
+CVX_HD void chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int vi, int num, float scalefac, GetB getb, PutV put)
+{
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const bool st = ((mask >> p) & 1u) != 0;
+        const uint32_t b = (uint32_t)(A >> (8 * p)) & 0xFFu;
+        const int c = (int)(int8_t)b;
+        const uint32_t op = chunk8_operand(A, N, p);
+        const bool lit = c > VLESC2 && c < RLESC3;
+        const bool single = lit || c == VLESC2 || c == VLESC3 || c == VLESC4;
+        int q = c;
+        q = (c == VLESC2) ? (int)(int16_t)(op & 0xFFFFu) : q;
+        q = (c == VLESC3) ? ((int)(op << 8) >> 8) : q;
+        float fv = (float)q;
+        if (c == VLESC4) {
+#ifdef __CUDA_ARCH__
+            fv = __uint_as_float(op);
+#else
+            memcpy(&fv, &op, 4);
+#endif
+        }
+        if (st && single && !(lit && c == 0) && vi < num) put(vi, CVX_MUL(fv, scalefac));
+        if (st && (c == VLESC2_8x || c == VLESC3_8x)) {
+            const int k = base + p + 1;
+            const int w = (c == VLESC2_8x) ? 2 : 3;
+            for (int j = 0; j < 8 && vi + j < num; ++j) {
+                int v;
+                if (w == 2) v = (int)(int16_t)(getb(k + 2 * j) | (getb(k + 2 * j + 1) << 8));
+                else v = (int)((uint32_t)getb(k + 3 * j) << 8 | (uint32_t)getb(k + 3 * j + 1) << 16 | (uint32_t)getb(k + 3 * j + 2) << 24) >> 8;
+                put(vi + j, CVX_MUL(scalefac, (float)v));
+            }
+        }
+        int adv = 8;
+        adv = single ? 1 : adv;
+        adv = (c == RLESC1) ? (int)(op & 0xFFu) : adv;
+        adv = (c == RLESC3) ? (int)(op & 0xFFFFFFu) : adv;
+        vi += st ? adv : 0;
     }
 }
 

@@ -150,5 +150,58 @@ extern "C" int emu_rle_decode(float mulfac, float* vals, int num, const uint8_t*
     return repairs;
 }
 
+// decode with the 8-byte chunk formulation of k_decode32: windows of `nch_max` chunks, speculation from the two
+// previous chunks, chain verification/repair, clamped counts, exclusive scan, expansion.  `hint` = payload bytes
+// of this block when known (limits the first window), 0 = unknown.  Returns repair rounds or a negative error.
+extern "C" int emu_rle_decode8(float mulfac, float* vals, int num, const uint8_t* buf, long off, long buflen, int nch_max, long hint)
+{
+    float scalefac = 1.0f / mulfac;
+    for (int i = 0; i < num; ++i) vals[i] = 0.0f;
+    long cb = off & ~15L;                     // window base (16-byte aligned, as the cp.async staging needs)
+    int entry = (int)(off - cb);
+    int produced = 0, repairs = 0;
+    auto getb = [&](long k) -> uint32_t { return (k >= 0 && k < buflen) ? buf[k] : 0u; };
+    auto load64 = [&](long byte0) { uint64_t x = 0; for (int j = 0; j < 8; ++j) x |= (uint64_t)getb(byte0 + j) << (8 * j); return x; };
+    while (produced < num) {
+        int nch = nch_max;
+        if (hint > 0) { long want = (entry + hint + 7) >> 3; want += want & 1; if (want < nch) nch = (int)want; }
+        std::vector<int> ent(nch), ext(nch), cnt(nch);
+        std::vector<uint32_t> mask(nch);
+        std::vector<uint64_t> A(nch), N(nch);
+        for (int c = 0; c < nch; ++c) {
+            A[c] = load64(cb + 8L * c); N[c] = load64(cb + 8L * c + 8);
+            int d, dummy = 0;
+            if (c == 0) d = entry;
+            else if (c == 1) { d = entry; chunk8_walk<false>(load64(cb), 0, d, dummy); }
+            else { d = 0; chunk8_walk<false>(load64(cb + 8L * (c - 2)), 0, d, dummy); chunk8_walk<false>(load64(cb + 8L * (c - 1)), 0, d, dummy); }
+            ent[c] = d; cnt[c] = 0;
+            mask[c] = chunk8_walk<true>(A[c], N[c], d, cnt[c]);
+            ext[c] = d;
+        }
+        for (;;) {
+            bool bad = false;
+            std::vector<int> fix(nch, -1);
+            for (int c = 1; c < nch; ++c) if (ent[c] != ext[c - 1]) { fix[c] = ext[c - 1]; bad = true; }
+            if (!bad) break;
+            ++repairs;
+            for (int c = 1; c < nch; ++c) if (fix[c] >= 0) { int d = fix[c]; ent[c] = d; cnt[c] = 0; mask[c] = chunk8_walk<true>(A[c], N[c], d, cnt[c]); ext[c] = d; }
+        }
+        long vi = produced;
+        for (int c = 0; c < nch; ++c) {
+            int n = cnt[c] > (1 << 20) ? (1 << 20) : cnt[c];
+            if (vi < num)
+                chunk8_expand(mask[c], A[c], N[c], 8 * c, (int)vi, num, scalefac, [&](int k) { return getb(cb + k); },
+                              [&](int i, float v) { vals[i] = v; });
+            vi += n;
+        }
+        produced = vi > (1 << 30) ? (1 << 30) : (int)vi;
+        entry = ext[nch - 1];
+        cb += 8L * nch;
+        hint = 0;
+        if (cb > buflen + 64 && produced < num) return -3;
+    }
+    return repairs;
+}
+
 extern "C" int emu_token_len(int b) { return token_len((uint32_t)(b & 0xFF)); }
 extern "C" int emu_quantise(float f) { return quantise(f); }

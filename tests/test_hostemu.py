@@ -36,6 +36,7 @@ def emu():
     L.emu_wavelet.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     L.emu_rle_encode.argtypes = [C.c_float, _f32p, C.c_int, C.c_int, _u8p]
     L.emu_rle_decode.argtypes = [C.c_float, _f32p, C.c_int, C.c_void_p, C.c_long, C.c_long, C.c_int]
+    L.emu_rle_decode8.argtypes = [C.c_float, _f32p, C.c_int, C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_long]
     L.emu_quantise.argtypes = [C.c_float]
     return L
 
@@ -110,6 +111,29 @@ def test_speculative_decoder_equals_oracle(emu, name, off):
         rc = emu.emu_rle_decode(mulfac, got, n, buf.ctypes.data, off, len(buf), nthreads)
         assert rc >= 0
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("name", list(_rle_cases().keys()))
+@pytest.mark.parametrize("off", [0, 5, 16, 27])
+def test_chunk8_decoder_equals_oracle(emu, name, off):
+    """the 8-byte chunk formulation used by k_decode32, with exact, wrong (too short) and unknown length hints"""
+    vals = _rle_cases()[name]
+    n = len(vals)
+    mulfac = np.float32(0.37)
+    enc = np.zeros(5 * n + 64, np.uint8)
+    m = ol.oracle().cvxo_rle_encode(mulfac, vals, n, enc)
+    want = np.zeros(n, np.float32)
+    ol.oracle().cvxo_rle_decode(mulfac, want, n, enc)
+    rng = np.random.default_rng(off + 100)
+    buf = ol.aligned_u8(off + m + 16384)
+    buf[:] = rng.integers(0, 256, len(buf), dtype=np.uint8)
+    buf[off:off + m] = enc[:m]
+    for nch in (2, 16, 1024):
+        for hint in (m, max(1, m // 3), 0):
+            got = np.full(n, 7.0, np.float32)
+            rc = emu.emu_rle_decode8(mulfac, got, n, buf.ctypes.data, off, len(buf), nch, hint)
+            assert rc >= 0, (nch, hint, rc)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (nch, hint)
 
 
 def test_quantise_matches_oracle(emu):
