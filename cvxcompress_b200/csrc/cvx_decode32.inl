@@ -143,6 +143,10 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
             }
             const int last_ext = s_ext[nch - 1];
             const int any = __syncthreads_or((bad[0] || bad[1]) ? 1 : 0);
+#ifdef CVX_PHASE_TIMING
+            if (tid == 0) atomicAdd(&g_phase[1][10], 1ull);
+            if (bad[0] || bad[1]) atomicAdd(&g_phase[1][11], 1ull);
+#endif
             if (!any) { entry = last_ext; break; }
 #pragma unroll
             for (int j = 0; j < 2; ++j)
@@ -188,12 +192,14 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
 #pragma unroll
         for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    CVX_PH_DECL;
     for (;;) {
         const long tn = t + gridDim.x;
         D32Src nxt = cur;
         if (tn < p.nblk) nxt = d32_locate(p, tn);                   // table reads overlap the parse below
         cp_async_wait_all();
         __syncthreads();                                            // window staged, block buffer zeroed
+        CVX_PH(0);
         if (cur.raw) {                                              // CvxCompress.cpp:555: B fp32 coefficients
             for (int i = tid; i < F32_B; i += D32_T) {
                 uint32_t u = 0;
@@ -206,13 +212,16 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
             d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, [&](int i, float v) { sm[physr(i, 5)] = v; });
         }
         __syncthreads();
+        CVX_PH(1);
         if (tn < p.nblk)                                            // next block's payload streams in under the transform
             d32_issue_window(s_win + (buf ^ 1) * D32_WIN,
                              reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi);
         f32_pass_x<EXACT, false>(sm);
         __syncthreads();
+        CVX_PH(2);
         f32_pass_y<EXACT, false>(sm);
         __syncthreads();
+        CVX_PH(3);
         float v[2][32];
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
@@ -221,6 +230,7 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
             for (int r = 0; r < 32; ++r) v[k][r] = zl[reg_to_sub<32, EXACT>(r) * 1024];
         }
         __syncthreads();                                            // every z line is in registers
+        CVX_PH(4);
         {
             float4* z4 = reinterpret_cast<float4*>(sm);
 #pragma unroll
@@ -236,15 +246,21 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
             inv_line<32, EXACT>(v[k]);
             const int gy = iiy * 32 + warp + 16 * k;
             if (gx < p.g.nx && gy < p.g.ny) {
-                float* dst = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
+                float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
+                if (nzl == 32) {                                    // interior block: 32 unconditional row stores
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < nzl) dst[j * plane] = v[k][j];
+                    for (int j = 0; j < 32; ++j) { *dp = v[k][j]; dp += plane; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { if (j < nzl) *dp = v[k][j]; dp += plane; }
+                }
             }
         }
+        CVX_PH(5);
         if (tn >= p.nblk) break;
         t = tn;
         cur = nxt;
         buf ^= 1;
     }
+    CVX_PH_FLUSH(1);
 }

@@ -18,4 +18,6 @@ for kind, name, fn in ((0, "encode", lambda: api.compress_device(vol, 32, 32, 32
     n = L.cvx_debug_phases(out, kind, 1)
     v = list(out)[:12]; tot = sum(v) or 1
     nblk = 33 * 39 * ((nz + 31) // 32)
-    print(name, mode, "cycles/block %.0f" % (tot / nblk), " ".join("%d:%.1f%%" % (i, 100.0 * x / tot) for i, x in enumerate(v)))
+    extra = list(out)[10:12]
+    tot -= sum(extra)
+    print(name, mode, "counters/block %.2f %.2f" % (extra[0] / nblk, extra[1] / nblk), "cycles/block %.0f" % (tot / nblk), " ".join("%d:%.1f%%" % (i, 100.0 * x / tot) for i, x in enumerate(v)))
