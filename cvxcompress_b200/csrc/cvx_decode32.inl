@@ -74,11 +74,14 @@ struct D32Src {
 __device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
 {
     D32Src r;
-    unsigned long long o = p.offs[t];
+    unsigned long long o, o1 = 0;
+    // volatile: issued where written (the loop top), so the latency hides under the parse instead of in front of the prefetch
+    asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(o) : "l"(p.offs + t));
+    if (t + 1 < p.nblk) asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(o1) : "l"(p.offs + t + 1));
     r.raw = (int)(o >> 63);
     o &= 0x7FFFFFFFFFFFFFFFull;
     r.src = p.payload + o;
-    long nxt = (t + 1 < p.nblk) ? (long)(p.offs[t + 1] & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
+    long nxt = (t + 1 < p.nblk) ? (long)(o1 & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
     long h = nxt - (long)o;
     r.hint = (h > 0 && h <= 5L * F32_B + 8) ? h : 0;
     const float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
@@ -97,7 +100,7 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
     long hint = b.hint;
     int produced = 0;
     const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
-    auto getb = [&](int k) -> uint32_t { return (uint32_t)win[k]; };
+    auto getb = [win](int k) -> uint32_t { return (uint32_t)win[k]; };
     for (bool first = true;; first = false) {
         if (!first) {                     // rare: payload longer than one window, or a wrong hint
             __syncthreads();
@@ -209,7 +212,7 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                 sm[physr(i, 5)] = __uint_as_float(u);
             }
         } else {
-            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, [&](int i, float v) { sm[physr(i, 5)] = v; });
+            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, [sm](int i, float v) { sm[physr(i, 5)] = v; });
         }
         __syncthreads();
         CVX_PH(1);
@@ -219,15 +222,14 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
         f32_pass_x<EXACT, false>(sm);
         __syncthreads();
         CVX_PH(2);
-        f32_pass_y<EXACT, false>(sm);
+        f32_pass_y2<EXACT, false>(sm);
         __syncthreads();
         CVX_PH(3);
-        float v[2][32];
+        typename PairOf<EXACT>::type v[32];                         // z lines (x = lane, y = warp) and (x, y + 16), packed
+        {
+            const float* zl = f32_zline(sm, tid);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const float* zl = f32_zline(sm, tid + D32_T * k);
-#pragma unroll
-            for (int r = 0; r < 32; ++r) v[k][r] = zl[reg_to_sub<32, EXACT>(r) * 1024];
+            for (int r = 0; r < 32; ++r) p_set(v[r], zl[reg_to_sub<32, EXACT>(r) * 1024], zl[reg_to_sub<32, EXACT>(r) * 1024 + 512]);
         }
         __syncthreads();                                            // every z line is in registers
         CVX_PH(4);
@@ -241,18 +243,18 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
         const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
         const int gx = iix * 32 + lane, gz0 = iiz * 32;
         const int nzl = min(32, p.g.nz - gz0);
+        inv_line<32, EXACT>(v);
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            inv_line<32, EXACT>(v[k]);
             const int gy = iiy * 32 + warp + 16 * k;
             if (gx < p.g.nx && gy < p.g.ny) {
                 float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
                 if (nzl == 32) {                                    // interior block: 32 unconditional row stores
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) { *dp = v[k][j]; dp += plane; }
+                    for (int j = 0; j < 32; ++j) { *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
                 } else {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) { if (j < nzl) *dp = v[k][j]; dp += plane; }
+                    for (int j = 0; j < 32; ++j) { if (j < nzl) *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
                 }
             }
         }

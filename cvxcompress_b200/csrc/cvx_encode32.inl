@@ -130,24 +130,24 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         f32_pass_x<EXACT, true>(sm);
         __syncthreads();
         CVX_PH(1);
-        f32_pass_y<EXACT, true>(sm);
+        f32_pass_y2<EXACT, true>(sm);
         __syncthreads();
         CVX_PH(2);
         // z lines stay in registers: thread-line l = tid + 512 k is (x = lane, y = warp + 16 k)
-        float v[2][32];
+        typename PairOf<EXACT>::type vz[32];
+        {
+            const float* zl = f32_zline(sm, tid);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const float* zl = f32_zline(sm, tid + F32_T * k);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[k][j] = zl[j * 1024];
-            fwd_line<32, EXACT>(v[k]);
+            for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
+            fwd_line<32, EXACT>(vz);
         }
+#define V_(k, r) ((k) ? p_hi(vz[r]) : p_lo(vz[r]))
         auto write_back = [&]() {
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
                 float* zl = f32_zline(sm, tid + F32_T * k);
 #pragma unroll
-                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = v[k][r];
+                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = V_(k, r);
             }
         };
         bool in_smem = false;
@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             for (int k = 0; k < 2; ++k)
 #pragma unroll
                 for (int r = 0; r < 32; ++r) {
-                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(v[k][r]) <= T));
+                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(V_(k, r)) <= T));
                     if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
                 }
             __syncthreads();
@@ -217,13 +217,13 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             for (int k = 0; k < 2; ++k)
 #pragma unroll
                 for (int r = 0; r < 32; ++r) {
-                    const bool nz = !(fabsf(v[k][r]) <= T);
+                    const bool nz = !(fabsf(V_(k, r)) <= T);
                     const unsigned m = __ballot_sync(0xffffffffu, nz);
                     // unconditional (broadcast) load of the row base: 64 independent loads pipeline instead of
                     // 64 dependent load->store chains inside divergent branches
                     const int row = reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k;
                     const int at = s_base[row] + __popc(m & lt);
-                    if (nz) s_list[at] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(v[k][r]));
+                    if (nz) s_list[at] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(V_(k, r)));
                 }
         }
         __syncthreads();
@@ -288,3 +288,4 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     complete_pending();
     CVX_PH_FLUSH(0);
 }
+#undef V_

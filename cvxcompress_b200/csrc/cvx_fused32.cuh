@@ -149,6 +149,41 @@ __device__ __forceinline__ void f32_pass_y(float* sm)
     }
 }
 
+// y lines, two per thread side by side in packed registers: lines (x = lane, z = warp) and (x, z + 16) are
+// 16384 floats apart with the same swizzle, so both come from the same eight base pointers (FADD2/FFMA2 math)
+template <bool EXACT, bool FWD>
+__device__ __forceinline__ void f32_pass_y2(float* sm)
+{
+    const int x = threadIdx.x & 31, z = threadIdx.x >> 5;
+    float* a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = sm + z * 1024 + (x ^ (k << 2));
+    typename PairOf<EXACT>::type v[32];
+    if (FWD) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) p_set(v[j], a[j & 7][j * 32], a[j & 7][j * 32 + 16384]);
+        fwd_line<32, EXACT>(v);
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const int s = reg_to_sub<32, EXACT>(r);
+            a[s & 7][s * 32] = p_lo(v[r]);
+            a[s & 7][s * 32 + 16384] = p_hi(v[r]);
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const int s = reg_to_sub<32, EXACT>(r);
+            p_set(v[r], a[s & 7][s * 32], a[s & 7][s * 32 + 16384]);
+        }
+        inv_line<32, EXACT>(v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            a[j & 7][j * 32] = p_lo(v[j]);
+            a[j & 7][j * 32 + 16384] = p_hi(v[j]);
+        }
+    }
+}
+
 // z line of thread-line l (x = l & 31, y = l >> 5): element j at j*1024 + y*32 + (x ^ ((y & 7) << 2))
 __device__ __forceinline__ float* f32_zline(float* sm, int l)
 {

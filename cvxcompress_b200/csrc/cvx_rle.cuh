@@ -197,10 +197,16 @@ CVX_HD int seg_emit(int ngroups, float mulfac, int carry_in, int pos, bool flush
 // total length in bytes of the token whose first byte is b (Run_Length_Encode_Slow.cpp:415-513)
 CVX_HD int token_len(uint32_t b)
 {
-    uint32_t i = b - 0x7Du;     // 0x7D RLESC3, 0x7E VLESC3_8x, 0x7F RLESC1, 0x80 VLESC4, 0x81 VLESC3, 0x82 VLESC2_8x, 0x83 VLESC2
-    uint32_t lo = 0x05021904u, hi = 0x00031104u;
-    uint32_t t = i < 4u ? lo >> (8u * i) : hi >> (8u * (i & 3u));
-    return i < 7u ? (int)(t & 0xFFu) : 1;
+    // 0x7D RLESC3 4, 0x7E VLESC3_8x 25, 0x7F RLESC1 2, 0x80 VLESC4 5, 0x81 VLESC3 4, 0x82 VLESC2_8x 17, 0x83 VLESC2 3, else 1:
+    // an 8-entry byte table indexed by min(b - 0x7D, 7) (PRMT on the device)
+    uint32_t i = b - 0x7Du;
+    i = i < 7u ? i : 7u;
+#ifdef __CUDA_ARCH__
+    return (int)(__byte_perm(0x05021904u, 0x01031104u, i) & 0xFFu);
+#else
+    const uint64_t tbl = 0x0103110405021904ull;
+    return (int)((tbl >> (8u * i)) & 0xFFu);
+#endif
 }
 
 // Walk one 16-byte chunk.  d = bytes until the next token start (0 == a token starts at
@@ -336,9 +342,43 @@ CVX_HD uint32_t chunk8_walk(uint64_t A, uint64_t N, int& d, int& n)
     return mask;
 }
 
+// the tokens that are neither a literal nor RLESC1: kept out of line so that the unrolled fast path stays small
+// (the expansion is instruction-cache bound otherwise).  k = window index of the token's first operand byte.
+#ifdef __CUDACC__
+#define CVX_HD_NOINLINE __host__ __device__ __noinline__
+#else
+#define CVX_HD_NOINLINE
+#endif
+template <class GetB, class PutV>
+CVX_HD_NOINLINE int chunk8_rare(int c, uint32_t op, int k, int vi, int num, float scalefac, GetB getb, PutV put)
+{
+    if (c == RLESC3) return (int)(op & 0xFFFFFFu);
+    if (c == VLESC2_8x || c == VLESC3_8x) {
+        for (int j = 0; j < 8 && vi + j < num; ++j) {
+            int v;
+            if (c == VLESC2_8x) v = (int)(int16_t)(getb(k + 2 * j) | (getb(k + 2 * j + 1) << 8));
+            else v = (int)((uint32_t)getb(k + 3 * j) << 8 | (uint32_t)getb(k + 3 * j + 1) << 16 | (uint32_t)getb(k + 3 * j + 2) << 24) >> 8;
+            put(vi + j, CVX_MUL(scalefac, (float)v));
+        }
+        return 8;
+    }
+    float fv;
+    if (c == VLESC4) {
+#ifdef __CUDA_ARCH__
+        fv = __uint_as_float(op);
+#else
+        memcpy(&fv, &op, 4);
+#endif
+    } else {
+        fv = (float)((c == VLESC2) ? (int)(int16_t)(op & 0xFFFFu) : ((int)(op << 8) >> 8));
+    }
+    if (vi < num) put(vi, CVX_MUL(fv, scalefac));
+    return 1;
+}
+
 // Write the values of the tokens that start in this chunk (Run_Length_Encode_Slow.cpp:415-513).  vi = raster index
 // of the first value; zeros are not written (pre-zeroed destination).  getb(k) = byte k of the staged window,
-// base = window index of this chunk's first byte (used by the rare 17/25-byte tokens only).
+// base = window index of this chunk's first byte.  getb / put must be cheap to copy (they are passed by value).
 template <class GetB, class PutV>
 CVX_HD void chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int vi, int num, float scalefac, GetB getb, PutV put)
 {
@@ -347,35 +387,17 @@ CVX_HD void chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int v
         const bool st = ((mask >> p) & 1u) != 0;
         const uint32_t b = (uint32_t)(A >> (8 * p)) & 0xFFu;
         const int c = (int)(int8_t)b;
+        const bool lit = (uint32_t)(c + 124) <= 248u;                 // -124 .. 124: one value, the byte itself
         const uint32_t op = chunk8_operand(A, N, p);
-        const bool lit = c > VLESC2 && c < RLESC3;
-        const bool single = lit || c == VLESC2 || c == VLESC3 || c == VLESC4;
+        // literal, VLESC2 and VLESC3 (the head of a block is dense in the latter two) without divergence
+        const bool v2 = (c == VLESC2), v3 = (c == VLESC3);
         int q = c;
-        q = (c == VLESC2) ? (int)(int16_t)(op & 0xFFFFu) : q;
-        q = (c == VLESC3) ? ((int)(op << 8) >> 8) : q;
-        float fv = (float)q;
-        if (c == VLESC4) {
-#ifdef __CUDA_ARCH__
-            fv = __uint_as_float(op);
-#else
-            memcpy(&fv, &op, 4);
-#endif
-        }
-        if (st && single && !(lit && c == 0) && vi < num) put(vi, CVX_MUL(fv, scalefac));
-        if (st && (c == VLESC2_8x || c == VLESC3_8x)) {
-            const int k = base + p + 1;
-            const int w = (c == VLESC2_8x) ? 2 : 3;
-            for (int j = 0; j < 8 && vi + j < num; ++j) {
-                int v;
-                if (w == 2) v = (int)(int16_t)(getb(k + 2 * j) | (getb(k + 2 * j + 1) << 8));
-                else v = (int)((uint32_t)getb(k + 3 * j) << 8 | (uint32_t)getb(k + 3 * j + 1) << 16 | (uint32_t)getb(k + 3 * j + 2) << 24) >> 8;
-                put(vi + j, CVX_MUL(scalefac, (float)v));
-            }
-        }
-        int adv = 8;
-        adv = single ? 1 : adv;
-        adv = (c == RLESC1) ? (int)(op & 0xFFu) : adv;
-        adv = (c == RLESC3) ? (int)(op & 0xFFFFFFu) : adv;
+        q = v2 ? (int)(int16_t)(op & 0xFFFFu) : q;
+        q = v3 ? ((int)(op << 8) >> 8) : q;
+        const bool single = lit || v2 || v3;
+        if (st && single && q != 0 && vi < num) put(vi, CVX_MUL((float)q, scalefac));
+        int adv = (c == RLESC1) ? (int)(op & 0xFFu) : 1;
+        if (st && !single && c != RLESC1) adv = chunk8_rare(c, op, base + p + 1, vi, num, scalefac, getb, put);
         vi += st ? adv : 0;
     }
 }

@@ -14,6 +14,7 @@
 // Mirror rules: MIRR / MIRR_SL / MIRR_SH, Wavelet_Transform_Slow.cpp:59-67, :178-199.
 #pragma once
 #include <cuda_runtime.h>
+#include <string.h>
 
 #ifndef CVX_HD
 #define CVX_HD __host__ __device__ __forceinline__
@@ -89,13 +90,102 @@ CVX_HD constexpr int mirr_sh(int v, int nl, int nh)
 }
 
 // ------------------------------------------------------------------------------------------
+// Value types of the register-resident line transforms: `float` = one line, `F2` = two independent
+// lines side by side in one 64-bit register pair, computed with the Blackwell packed-fp32 instructions
+// (add/mul/fma.rn.f32x2 -> FADD2 / FMUL2 / FFMA2: one issue slot for both lines, same IEEE rounding as
+// the scalar instructions, so EXACT stays bit-exact).  The host build keeps the pair as two floats.
+// ------------------------------------------------------------------------------------------
+struct F2 {
+    unsigned long long u;
+};
+CVX_HD F2 f2_make(float x, float y)
+{
+    F2 r;
+#ifdef __CUDA_ARCH__
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.u) : "f"(x), "f"(y));
+#else
+    unsigned int a, b;
+    memcpy(&a, &x, 4); memcpy(&b, &y, 4);
+    r.u = (unsigned long long)a | ((unsigned long long)b << 32);
+#endif
+    return r;
+}
+CVX_HD float f2_lo(F2 v)
+{
+#ifdef __CUDA_ARCH__
+    float x, y;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v.u));
+    return x;
+#else
+    unsigned int a = (unsigned int)v.u; float x; memcpy(&x, &a, 4); return x;
+#endif
+}
+CVX_HD float f2_hi(F2 v)
+{
+#ifdef __CUDA_ARCH__
+    float x, y;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v.u));
+    return y;
+#else
+    unsigned int a = (unsigned int)(v.u >> 32); float x; memcpy(&x, &a, 4); return x;
+#endif
+}
+CVX_HD float v_add(float a, float b) { return CVX_ADD(a, b); }
+CVX_HD float v_mulc(float c, float a) { return CVX_MUL(c, a); }
+CVX_HD float v_fmac(float c, float a, float b) { return CVX_FMA(c, a, b); }      // c * a + b
+CVX_HD F2 v_add(F2 a, F2 b)
+{
+#ifdef __CUDA_ARCH__
+    F2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d.u) : "l"(a.u), "l"(b.u)); return d;
+#else
+    return f2_make(CVX_ADD(f2_lo(a), f2_lo(b)), CVX_ADD(f2_hi(a), f2_hi(b)));
+#endif
+}
+CVX_HD F2 v_mulc(float c, F2 a)
+{
+#ifdef __CUDA_ARCH__
+    F2 d; const F2 cc = f2_make(c, c);
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d.u) : "l"(cc.u), "l"(a.u)); return d;
+#else
+    return f2_make(CVX_MUL(c, f2_lo(a)), CVX_MUL(c, f2_hi(a)));
+#endif
+}
+CVX_HD F2 v_fmac(float c, F2 a, F2 b)
+{
+#ifdef __CUDA_ARCH__
+    F2 d; const F2 cc = f2_make(c, c);
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d.u) : "l"(cc.u), "l"(a.u), "l"(b.u)); return d;
+#else
+    return f2_make(CVX_FMA(c, f2_lo(a), f2_lo(b)), CVX_FMA(c, f2_hi(a), f2_hi(b)));
+#endif
+}
+
+// S2: two lines side by side computed with SCALAR instructions.  EXACT mode uses it instead of F2 because ptxas
+// (12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under --fmad=false, which would break bit-exactness
+// against the reference's separate multiply and add (Wavelet_Transform_Slow.cpp:418-448).
+struct S2 {
+    float x, y;
+};
+CVX_HD S2 v_add(S2 a, S2 b) { S2 r; r.x = CVX_ADD(a.x, b.x); r.y = CVX_ADD(a.y, b.y); return r; }
+CVX_HD S2 v_mulc(float c, S2 a) { S2 r; r.x = CVX_MUL(c, a.x); r.y = CVX_MUL(c, a.y); return r; }
+CVX_HD S2 v_fmac(float c, S2 a, S2 b) { S2 r; r.x = CVX_FMA(c, a.x, b.x); r.y = CVX_FMA(c, a.y, b.y); return r; }
+template <bool EXACT> struct PairOf { typedef F2 type; };
+template <> struct PairOf<true> { typedef S2 type; };
+CVX_HD void p_set(F2& d, float x, float y) { d = f2_make(x, y); }
+CVX_HD void p_set(S2& d, float x, float y) { d.x = x; d.y = y; }
+CVX_HD float p_lo(F2 v) { return f2_lo(v); }
+CVX_HD float p_hi(F2 v) { return f2_hi(v); }
+CVX_HD float p_lo(S2 v) { return v.x; }
+CVX_HD float p_hi(S2 v) { return v.y; }
+
+// ------------------------------------------------------------------------------------------
 // EXACT, register-resident.  One level on v[0..N): low half then high half (out-of-place
 // semantics through the copy t[]).
 // ------------------------------------------------------------------------------------------
-template <int N>
-CVX_HD void fwd_exact_level(float* v)
+template <int N, class V>
+CVX_HD void fwd_exact_level(V* v)
 {
-    float t[N];
+    V t[N];
 #pragma unroll
     for (int i = 0; i < N; ++i) t[i] = v[i];
     constexpr int nh = N / 2;
@@ -103,60 +193,60 @@ CVX_HD void fwd_exact_level(float* v)
     for (int ix = 0; ix < nh; ++ix) {
         {
             const int i0 = 2 * ix;
-            float acc = CVX_MUL(CVX_AL4, CVX_ADD(t[mirr(i0 - 4, N)], t[mirr(i0 + 4, N)]));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AL3, CVX_ADD(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AL2, CVX_ADD(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AL1, CVX_ADD(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AL0, t[i0]));
+            V acc = v_mulc(CVX_AL4, v_add(t[mirr(i0 - 4, N)], t[mirr(i0 + 4, N)]));
+            acc = v_add(acc, v_mulc(CVX_AL3, v_add(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)])));
+            acc = v_add(acc, v_mulc(CVX_AL2, v_add(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
+            acc = v_add(acc, v_mulc(CVX_AL1, v_add(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
+            acc = v_add(acc, v_mulc(CVX_AL0, t[i0]));
             v[ix] = acc;
         }
         {
             const int i0 = 2 * ix + 1;
-            float acc = CVX_MUL(CVX_AH3, CVX_ADD(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)]));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AH2, CVX_ADD(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AH1, CVX_ADD(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_AH0, t[i0]));
+            V acc = v_mulc(CVX_AH3, v_add(t[mirr(i0 - 3, N)], t[mirr(i0 + 3, N)]));
+            acc = v_add(acc, v_mulc(CVX_AH2, v_add(t[mirr(i0 - 2, N)], t[mirr(i0 + 2, N)])));
+            acc = v_add(acc, v_mulc(CVX_AH1, v_add(t[mirr(i0 - 1, N)], t[mirr(i0 + 1, N)])));
+            acc = v_add(acc, v_mulc(CVX_AH0, t[i0]));
             v[nh + ix] = acc;
         }
     }
 }
 
-template <int N>
-CVX_HD void inv_exact_level(float* v)
+template <int N, class V>
+CVX_HD void inv_exact_level(V* v)
 {
-    float t[N];
+    V t[N];
 #pragma unroll
     for (int i = 0; i < N; ++i) t[i] = v[i];
     constexpr int nh = N / 2, nl = N - nh;
 #pragma unroll
     for (int k = 0; k < nl; ++k) {
         {   // even sample 2k
-            float acc = CVX_MUL(CVX_SH3, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)]));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SL2, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 1, nl)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SH1, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k, nl, nh)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SL0, t[k]));
+            V acc = v_mulc(CVX_SH3, v_add(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)]));
+            acc = v_add(acc, v_mulc(CVX_SL2, v_add(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 1, nl)])));
+            acc = v_add(acc, v_mulc(CVX_SH1, v_add(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k, nl, nh)])));
+            acc = v_add(acc, v_mulc(CVX_SL0, t[k]));
             v[2 * k] = acc;
         }
         {   // odd sample 2k+1
-            float acc = CVX_MUL(CVX_SH4, CVX_ADD(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 2, nl, nh)]));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SL3, CVX_ADD(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 2, nl)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SH2, CVX_ADD(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SL1, CVX_ADD(t[mirr_sl(k, nl)], t[mirr_sl(k + 1, nl)])));
-            acc = CVX_ADD(acc, CVX_MUL(CVX_SH0, t[nl + k]));
+            V acc = v_mulc(CVX_SH4, v_add(t[mirr_sh(nl + k - 2, nl, nh)], t[mirr_sh(nl + k + 2, nl, nh)]));
+            acc = v_add(acc, v_mulc(CVX_SL3, v_add(t[mirr_sl(k - 1, nl)], t[mirr_sl(k + 2, nl)])));
+            acc = v_add(acc, v_mulc(CVX_SH2, v_add(t[mirr_sh(nl + k - 1, nl, nh)], t[mirr_sh(nl + k + 1, nl, nh)])));
+            acc = v_add(acc, v_mulc(CVX_SL1, v_add(t[mirr_sl(k, nl)], t[mirr_sl(k + 1, nl)])));
+            acc = v_add(acc, v_mulc(CVX_SH0, t[nl + k]));
             v[2 * k + 1] = acc;
         }
     }
 }
 
 // levels N, N/2, ..., 2 (Wavelet_Transform_Fast.cpp:48-55) / 2, ..., N (:183-190)
-template <int N>
-CVX_HD void fwd_exact(float* v)
+template <int N, class V>
+CVX_HD void fwd_exact(V* v)
 {
     fwd_exact_level<N>(v);
     if constexpr (N > 2) fwd_exact<N / 2>(v);
 }
-template <int N>
-CVX_HD void inv_exact(float* v)
+template <int N, class V>
+CVX_HD void inv_exact(V* v)
 {
     if constexpr (N > 2) inv_exact<N / 2>(v);
     inv_exact_level<N>(v);
@@ -167,51 +257,81 @@ CVX_HD void inv_exact(float* v)
 // the samples at positions S*j, j < N/S; evens are s_j, odds are d_j.  Boundary:
 // s_{m} -> s_{m-1}, d_{-1} -> d_0 (whole-sample symmetric extension == MIRR).
 // ------------------------------------------------------------------------------------------
-template <int N, int S>
-CVX_HD void fwd_lift_level(float* v)
+template <int N, int S, class V>
+CVX_HD void fwd_lift_level(V* v)
 {
     constexpr int m = N / S / 2;
 #define CVX_S(j) v[S * 2 * (j)]
 #define CVX_D(j) v[S * (2 * (j) + 1)]
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(CVX_LA, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+    for (int j = 0; j < m; ++j) CVX_D(j) = v_fmac(CVX_LA, v_add(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(CVX_LB, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+    for (int j = 0; j < m; ++j) CVX_S(j) = v_fmac(CVX_LB, v_add(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(CVX_LG, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+    for (int j = 0; j < m; ++j) CVX_D(j) = v_fmac(CVX_LG, v_add(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(CVX_LD, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
-#pragma unroll
-    for (int j = 0; j < m; ++j) { CVX_S(j) = CVX_MUL(CVX_S(j), CVX_ZL); CVX_D(j) = CVX_MUL(CVX_D(j), CVX_ZH); }
+    for (int j = 0; j < m; ++j) CVX_S(j) = v_fmac(CVX_LD, v_add(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
 }
-template <int N, int S>
-CVX_HD void inv_lift_level(float* v)
+template <int N, int S, class V>
+CVX_HD void inv_lift_level(V* v)
 {
     constexpr int m = N / S / 2;
 #pragma unroll
-    for (int j = 0; j < m; ++j) { CVX_S(j) = CVX_MUL(CVX_S(j), CVX_IZL); CVX_D(j) = CVX_MUL(CVX_D(j), CVX_IZH); }
+    for (int j = 0; j < m; ++j) CVX_S(j) = v_fmac(-CVX_LD, v_add(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(-CVX_LD, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
+    for (int j = 0; j < m; ++j) CVX_D(j) = v_fmac(-CVX_LG, v_add(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(-CVX_LG, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+    for (int j = 0; j < m; ++j) CVX_S(j) = v_fmac(-CVX_LB, v_add(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
 #pragma unroll
-    for (int j = 0; j < m; ++j) CVX_S(j) = CVX_FMA(-CVX_LB, CVX_ADD(CVX_D(j > 0 ? j - 1 : 0), CVX_D(j)), CVX_S(j));
-#pragma unroll
-    for (int j = 0; j < m; ++j) CVX_D(j) = CVX_FMA(-CVX_LA, CVX_ADD(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
+    for (int j = 0; j < m; ++j) CVX_D(j) = v_fmac(-CVX_LA, v_add(CVX_S(j), CVX_S(j + 1 < m ? j + 1 : m - 1)), CVX_D(j));
 #undef CVX_S
 #undef CVX_D
 }
-template <int N, int S = 1>
-CVX_HD void fwd_lift(float* v)
+// The two scalings of every level (low * ZL, high * ZH) are linear, so they are folded into ONE multiply per
+// coefficient after the last level (forward) / before the first (inverse): the sample at interleaved position
+// p = 2^(l-1) * odd is the high band of level l and carries ZL^(l-1) * ZH; position 0 carries ZL^levels.
+// 20 % fewer FP32 operations per line than scaling level by level; rounding differs in the last bits only.
+constexpr double lift_cpow(double b, int e) { double r = 1.0; for (int i = 0; i < e; ++i) r *= b; return r; }
+constexpr int lift_ctz(int p) { int n = 0; while (!(p & 1)) { p >>= 1; ++n; } return n; }
+constexpr int lift_log2(int n) { int l = 0; while (n > 1) { n >>= 1; ++l; } return l; }
+constexpr float lift_scale_fwd(int p, int N)
+{
+    return (float)(p == 0 ? lift_cpow((double)CVX_ZL, lift_log2(N)) : lift_cpow((double)CVX_ZL, lift_ctz(p)) * (double)CVX_ZH);
+}
+constexpr float lift_scale_inv(int p, int N)
+{
+    return (float)(p == 0 ? lift_cpow((double)CVX_IZL, lift_log2(N)) : lift_cpow((double)CVX_IZL, lift_ctz(p)) * (double)CVX_IZH);
+}
+template <int N, int P, bool FWD, class V>
+CVX_HD void lift_scale_all(V* v)
+{
+    constexpr float c = FWD ? lift_scale_fwd(P, N) : lift_scale_inv(P, N);      // compile-time: an immediate operand
+    v[P] = v_mulc(c, v[P]);
+    if constexpr (P + 1 < N) lift_scale_all<N, P + 1, FWD>(v);
+}
+template <int N, int S, class V>
+CVX_HD void fwd_lift_levels(V* v)
 {
     fwd_lift_level<N, S>(v);
-    if constexpr (N / S > 2) fwd_lift<N, S * 2>(v);
+    if constexpr (N / S > 2) fwd_lift_levels<N, S * 2>(v);
 }
-template <int N, int S = 1>
-CVX_HD void inv_lift(float* v)
+template <int N, int S, class V>
+CVX_HD void inv_lift_levels(V* v)
 {
-    if constexpr (N / S > 2) inv_lift<N, S * 2>(v);
+    if constexpr (N / S > 2) inv_lift_levels<N, S * 2>(v);
     inv_lift_level<N, S>(v);
+}
+template <int N, class V>
+CVX_HD void fwd_lift(V* v)
+{
+    fwd_lift_levels<N, 1>(v);
+    lift_scale_all<N, 0, true>(v);
+}
+template <int N, class V>
+CVX_HD void inv_lift(V* v)
+{
+    lift_scale_all<N, 0, false>(v);
+    inv_lift_levels<N, 1>(v);
 }
 
 // interleaved position p  <->  sub-band index (low first, recursively; DC at 0)
@@ -236,15 +356,42 @@ CVX_HD constexpr int lift_idx_to_pos(int i, int N)
 // SUB-BAND order after fwd / before inv for EXACT; for LIFT the sub-band side is addressed
 // through sub_pos<>(i): the register that holds sub-band coefficient i.
 // ------------------------------------------------------------------------------------------
-template <int N, bool EXACT>
-CVX_HD void fwd_line(float* v)
+template <int N, bool EXACT, class V>
+CVX_HD void fwd_line(V* v)
 {
     if constexpr (EXACT) fwd_exact<N>(v); else fwd_lift<N>(v);
 }
-template <int N, bool EXACT>
-CVX_HD void inv_line(float* v)
+template <int N, bool EXACT, class V>
+CVX_HD void inv_line(V* v)
 {
     if constexpr (EXACT) inv_exact<N>(v); else inv_lift<N>(v);
+}
+// S2: one line after the other (keeps the live register set at one line + its level copy)
+template <int N, bool EXACT>
+CVX_HD void fwd_line(S2* v)
+{
+    float a[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) a[i] = v[i].x;
+    fwd_line<N, EXACT>(a);
+#pragma unroll
+    for (int i = 0; i < N; ++i) { v[i].x = a[i]; a[i] = v[i].y; }
+    fwd_line<N, EXACT>(a);
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i].y = a[i];
+}
+template <int N, bool EXACT>
+CVX_HD void inv_line(S2* v)
+{
+    float a[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) a[i] = v[i].x;
+    inv_line<N, EXACT>(a);
+#pragma unroll
+    for (int i = 0; i < N; ++i) { v[i].x = a[i]; a[i] = v[i].y; }
+    inv_line<N, EXACT>(a);
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i].y = a[i];
 }
 // register index r -> sub-band index held there
 template <int N, bool EXACT>
