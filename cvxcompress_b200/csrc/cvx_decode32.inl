@@ -89,60 +89,82 @@ __device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
     return r;
 }
 
-// parse the block whose first window is already staged in `win`; writes coefficients through put(i, v)
+// per-thread result of walking its two chunks of a window
+struct D32Walk {
+    uint64_t A[2], N[2];
+    uint32_t mask[2];
+    int ent[2], ext[2], cnt[2];
+};
+
+__device__ __forceinline__ int d32_nchunks(int entry, long hint)
+{
+    int nch = D32_CH;
+    if (hint > 0) {
+        long want = (entry + hint + 7) >> 3;
+        want += want & 1;                 // even: the next window base stays 16-byte aligned
+        if (want < nch) nch = (int)want;
+    }
+    return nch;
+}
+
+// Speculative walk of this thread's chunks c = tid, tid + 512 of the staged window: entry state guessed from the two
+// chunks before it, then the chunk itself with value counting.  Straight-line code (selects, clamped loads, no
+// branches) so that the compiler can interleave it with the packed z-line arithmetic of the PREVIOUS block, whose
+// FFMA2/FADD2 stream leaves half of the issue slots free.
+__device__ __forceinline__ void d32_walk(const unsigned char* win, int entry, int nch, D32Walk& w)
+{
+    const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const int c = threadIdx.x + D32_T * j;
+        const bool act = c < nch;
+        const uint64_t P2 = w64[c >= 2 ? c - 2 : 0], P1 = w64[c >= 1 ? c - 1 : 0];
+        w.A[j] = w64[c]; w.N[j] = w64[c + 1];
+        int d = 0, dummy = 0;
+        chunk8_walk<false>(P2, 0ull, d, dummy);
+        d = (c == 1) ? entry : d;         // chunk 1: exact entry through chunk 0
+        chunk8_walk<false>(P1, 0ull, d, dummy);
+        d = (c == 0) ? entry : d;
+        w.ent[j] = d;
+        int cnt = 0;
+        const uint32_t m = chunk8_walk<true>(w.A[j], w.N[j], d, cnt);
+        w.mask[j] = act ? m : 0u;
+        w.cnt[j] = act ? cnt : 0;
+        w.ext[j] = act ? d : 0;
+    }
+}
+
+// parse the block whose first window is staged in `win` and already walked (`w`); writes coefficients through put(i, v)
 template <class PutV>
 __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, unsigned char* win, int* s_ext,
-                                          unsigned long long* scratch64, PutV put)
+                                          unsigned long long* scratch64, D32Walk& w, PutV put)
 {
     const int tid = threadIdx.x;
     const uint8_t* cbase = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(b.src) & ~(uintptr_t)15);
     int entry = (int)(b.src - cbase);
     long hint = b.hint;
     int produced = 0;
-    const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
     auto getb = [win](int k) -> uint32_t { return (uint32_t)win[k]; };
     for (bool first = true;; first = false) {
+        const int nch = d32_nchunks(entry, hint);
         if (!first) {                     // rare: payload longer than one window, or a wrong hint
             __syncthreads();
             d32_issue_window(win, cbase, hi);
             cp_async_wait_all();
             __syncthreads();
-        }
-        int nch = D32_CH;
-        if (hint > 0) {
-            long want = (entry + hint + 7) >> 3;
-            want += want & 1;             // even: the next window base stays 16-byte aligned
-            if (want < nch) nch = (int)want;
-        }
-        uint64_t A[2], N[2];
-        uint32_t mask[2];
-        int ent[2], ext[2], cnt[2];
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int c = tid + D32_T * j;
-            mask[j] = 0; ent[j] = 0; ext[j] = 0; cnt[j] = 0; A[j] = 0; N[j] = 0;
-            if (c < nch) {
-                A[j] = w64[c]; N[j] = w64[c + 1];
-                int d, dummy = 0;
-                if (c == 0) d = entry;
-                else if (c == 1) { d = entry; chunk8_walk<false>(w64[0], 0ull, d, dummy); }
-                else { d = 0; chunk8_walk<false>(w64[c - 2], 0ull, d, dummy); chunk8_walk<false>(w64[c - 1], 0ull, d, dummy); }
-                ent[j] = d;
-                mask[j] = chunk8_walk<true>(A[j], N[j], d, cnt[j]);
-                ext[j] = d;
-            }
+            d32_walk(win, entry, nch, w);
         }
         for (;;) {                        // verify exit(c-1) == entry(c); repair until the chain is consistent
 #pragma unroll
-            for (int j = 0; j < 2; ++j) { const int c = tid + D32_T * j; if (c < nch) s_ext[c] = ext[j]; }
+            for (int j = 0; j < 2; ++j) { const int c = tid + D32_T * j; if (c < nch) s_ext[c] = w.ext[j]; }
             __syncthreads();
             bool bad[2];
             int want[2];
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const int c = tid + D32_T * j;
-                want[j] = (c > 0 && c < nch) ? s_ext[c - 1] : ent[j];
-                bad[j] = want[j] != ent[j];
+                want[j] = (c > 0 && c < nch) ? s_ext[c - 1] : w.ent[j];
+                bad[j] = want[j] != w.ent[j];
             }
             const int last_ext = s_ext[nch - 1];
             const int any = __syncthreads_or((bad[0] || bad[1]) ? 1 : 0);
@@ -153,16 +175,16 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
             if (!any) { entry = last_ext; break; }
 #pragma unroll
             for (int j = 0; j < 2; ++j)
-                if (bad[j]) { int d = want[j]; ent[j] = d; cnt[j] = 0; mask[j] = chunk8_walk<true>(A[j], N[j], d, cnt[j]); ext[j] = d; }
+                if (bad[j]) { int d = want[j]; w.ent[j] = d; w.cnt[j] = 0; w.mask[j] = chunk8_walk<true>(w.A[j], w.N[j], d, w.cnt[j]); w.ext[j] = d; }
         }
-        const unsigned c0 = (unsigned)min(cnt[0], 1 << 20), c1 = (unsigned)min(cnt[1], 1 << 20);
+        const unsigned c0 = (unsigned)min(w.cnt[0], 1 << 20), c1 = (unsigned)min(w.cnt[1], 1 << 20);
         unsigned long long total;
         const unsigned long long ex = d32_excl_sum64((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
         const long tot0 = (long)(total & 0xFFFFFFFFull), tot1 = (long)(total >> 32);
         long vi0 = (long)produced + (long)(ex & 0xFFFFFFFFull);
         long vi1 = (long)produced + tot0 + (long)(ex >> 32);
-        if (mask[0] && vi0 < F32_B) chunk8_expand(mask[0], A[0], N[0], 8 * tid, (int)vi0, F32_B, b.scalefac, getb, put);
-        if (mask[1] && vi1 < F32_B) chunk8_expand(mask[1], A[1], N[1], 8 * (tid + D32_T), (int)vi1, F32_B, b.scalefac, getb, put);
+        if (w.mask[0] && vi0 < F32_B) chunk8_expand(w.mask[0], w.A[0], w.N[0], 8 * tid, (int)vi0, F32_B, b.scalefac, getb, put);
+        if (w.mask[1] && vi1 < F32_B) chunk8_expand(w.mask[1], w.A[1], w.N[1], 8 * (tid + D32_T), (int)vi1, F32_B, b.scalefac, getb, put);
         long np = (long)produced + tot0 + tot1;
         produced = np > (1 << 30) ? (1 << 30) : (int)np;
         if (produced >= F32_B) break;
@@ -195,15 +217,21 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
 #pragma unroll
         for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    D32Walk wk;
+    cp_async_wait_all();
+    __syncthreads();                                                // first window staged, block buffer zeroed
+    {
+        const int entry = (int)(reinterpret_cast<uintptr_t>(cur.src) & 15);
+        d32_walk(s_win, entry, d32_nchunks(entry, cur.hint), wk);
+    }
     CVX_PH_DECL;
     for (;;) {
         const long tn = t + gridDim.x;
         D32Src nxt = cur;
         if (tn < p.nblk) nxt = d32_locate(p, tn);                   // table reads overlap the parse below
-        cp_async_wait_all();
-        __syncthreads();                                            // window staged, block buffer zeroed
         CVX_PH(0);
         if (cur.raw) {                                              // CvxCompress.cpp:555: B fp32 coefficients
+            __syncthreads();                                        // every thread has zeroed its cells of the previous block
             for (int i = tid; i < F32_B; i += D32_T) {
                 uint32_t u = 0;
                 const uint8_t* s = cur.src + 4L * i;
@@ -212,37 +240,47 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                 sm[physr(i, 5)] = __uint_as_float(u);
             }
         } else {
-            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, [sm](int i, float v) { sm[physr(i, 5)] = v; });
+            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
         }
         __syncthreads();
         CVX_PH(1);
         if (tn < p.nblk)                                            // next block's payload streams in under the transform
             d32_issue_window(s_win + (buf ^ 1) * D32_WIN,
                              reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi);
+        // warp w owns the x rows AND the y lines of the z slices w and w + 16: no CTA barrier between the two passes,
+        // so warps drift apart and one warp's shared-memory traffic overlaps another's arithmetic
         f32_pass_x<EXACT, false>(sm);
-        __syncthreads();
+        __syncwarp();
         CVX_PH(2);
         f32_pass_y2<EXACT, false>(sm);
-        __syncthreads();
+        cp_async_wait_all();                                        // this thread's part of the next window has landed ...
+        __syncthreads();                                            // ... and everybody's; all y lines are written
         CVX_PH(3);
         typename PairOf<EXACT>::type v[32];                         // z lines (x = lane, y = warp) and (x, y + 16), packed
         {
-            const float* zl = f32_zline(sm, tid);
+            // each thread reads its two z lines and leaves zeros behind: the buffer is clean for the next block's
+            // expansion without another barrier or a separate fill pass
+            float* zl = f32_zline(sm, tid);
 #pragma unroll
-            for (int r = 0; r < 32; ++r) p_set(v[r], zl[reg_to_sub<32, EXACT>(r) * 1024], zl[reg_to_sub<32, EXACT>(r) * 1024 + 512]);
+            for (int r = 0; r < 32; ++r) {
+                float* e = zl + reg_to_sub<32, EXACT>(r) * 1024;
+                p_set(v[r], e[0], e[512]);
+            }
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
         }
-        __syncthreads();                                            // every z line is in registers
         CVX_PH(4);
-        {
-            float4* z4 = reinterpret_cast<float4*>(sm);
-#pragma unroll
-            for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
         const int iix = (int)(t % p.nbx);
         const long q = t / p.nbx;
         const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
         const int gx = iix * 32 + lane, gz0 = iiz * 32;
         const int nzl = min(32, p.g.nz - gz0);
+        {
+            // walk the NEXT block's chunks here: integer work that fills the issue slots the packed z-line arithmetic leaves
+            // free (no branch in between, so both streams are scheduled together)
+            const int entry = (int)(reinterpret_cast<uintptr_t>(nxt.src) & 15);
+            d32_walk(s_win + (buf ^ 1) * D32_WIN, entry, d32_nchunks(entry, nxt.hint), wk);
+        }
         inv_line<32, EXACT>(v);
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
@@ -251,7 +289,11 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                 float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
                 if (nzl == 32) {                                    // interior block: 32 unconditional row stores
 #pragma unroll
+#ifdef CVX_EXP_NOSTORE
+                    for (int j = 0; j < 32; ++j) { const float o = k ? p_hi(v[j]) : p_lo(v[j]); if (o != o) *dp = o; dp += plane; }
+#else
                     for (int j = 0; j < 32; ++j) { *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
+#endif
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) { if (j < nzl) *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }

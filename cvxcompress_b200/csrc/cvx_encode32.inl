@@ -78,6 +78,9 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     __shared__ unsigned int s_ticket[2];
     __shared__ unsigned long long s_off;
     __shared__ unsigned long long s_lb[F32_T / 32 + 2];
+    __shared__ int s_chunk[F32_LCAP / 32];
+    __shared__ unsigned short s_dq[F32_ROWS];
+    __shared__ int s_dqn;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -117,6 +120,10 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     for (int it = 0;; ++it) {
         const long t = s_ticket[it & 1];
         if (t >= p.nblk) break;
+        // the NEXT block's ticket is drawn now: the atomic's round trip hides under the transform instead of sitting
+        // in front of the prefetch
+        unsigned int nt = 0;
+        if (tid == 0) nt = atomicAdd(p.ticket, 1u);
         if (use_tma) {
             mbar_wait(&s_bar, parity);
             parity ^= 1u;
@@ -128,7 +135,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             __syncthreads();
         }
         f32_pass_x<EXACT, true>(sm);
-        __syncthreads();
+        __syncwarp();                    // warp w owns the x rows and the y lines of z slices w and w + 16: no CTA barrier needed
         CVX_PH(1);
         f32_pass_y2<EXACT, true>(sm);
         __syncthreads();
@@ -142,20 +149,17 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             fwd_line<32, EXACT>(vz);
         }
 #define V_(k, r) ((k) ? p_hi(vz[r]) : p_lo(vz[r]))
-        auto write_back = [&]() {
+        // The coefficients go back to the block buffer (one conflict-free store per cell); the coder below works on
+        // row masks and gathers the few non-zero values from there, which costs far fewer integer instructions
+        // (half-rate pipe) than compacting them out of the registers row by row.
+        float mulfac = gmul;
+        if (p.use_local) {                                       // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
                 float* zl = f32_zline(sm, tid + F32_T * k);
 #pragma unroll
                 for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = V_(k, r);
             }
-        };
-        bool in_smem = false;
-        float mulfac = gmul;
-        if (p.use_local) {                                       // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348
-            __syncthreads();
-            write_back();
-            in_smem = true;
             __syncthreads();
             const float ss = EXACT ? cta_sumsq_exact<F32_T>(F32_B, s_red, [&](int i) { return sm[physr(i, 5)]; })
                                    : cta_sumsq<F32_T>(sm, F32_B, s_red);
@@ -165,18 +169,23 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         }
         // ---- which coefficients quantise to non-zero: one compare per cell, one ballot per row ----
         const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
+        const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            float* zl = f32_zline(sm, tid + F32_T * k);
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                const float c = V_(k, r);
+                if (!p.use_local) zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
+                const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
+                if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+            }
+        }
+        __syncthreads();
+        CVX_PH(3);
+        // rows 2*tid, 2*tid+1 -> list positions (exclusive scan of the row populations)
         int n = F32_LCAP + 1;
         if (sparse_ok) {
-            const float T = nz_threshold(mulfac);
-#pragma unroll
-            for (int k = 0; k < 2; ++k)
-#pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(V_(k, r)) <= T));
-                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
-                }
-            __syncthreads();
-            CVX_PH(3);
             const int c0 = __popc(s_nzm[2 * tid]), c1 = __popc(s_nzm[2 * tid + 1]);
             const int base = cta_excl_sum<F32_T>(c0 + c1, scratch, n);
             s_base[2 * tid] = base;
@@ -184,8 +193,6 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         }
         if (n > F32_LCAP) {
             // ---- dense block: the CTA-wide coder on the shared-memory block (also raw fallback, CvxCompress.cpp:350-360) ----
-            __syncthreads();
-            if (!in_smem) write_back();
             __syncthreads();
             auto get8 = [&](int g, float* c) {
                 const int i = g * 8;
@@ -196,54 +203,96 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             encode_tail<F32_T>(p, t, sm, mulfac, get8, [](long i) { return (long)physr((int)i, 5); },
                                reinterpret_cast<int4*>(s_list), scratch, &s_off);
             if (tid == 0) {
-                const unsigned int nt = atomicAdd(p.ticket, 1u);
                 s_ticket[(it + 1) & 1] = nt;
                 if (use_tma && nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
             }
             __syncthreads();
             continue;
         }
-        // ---- sparse block ----
-        __syncthreads();                 // s_base complete; nobody reads the block buffer any more
+        // ---- sparse block: (index, value) list in raster order.  Thread t owns rows t and t + 512: a row with up to 4
+        //      non-zeros is unpacked by its thread; denser rows (they cluster in the low-z head of the block) are queued
+        //      and compacted by whole warps, one lane per cell, dealt round-robin so that no warp carries the head alone ----
+        if (tid == 0) s_dqn = 0;
+        __syncthreads();                 // s_base complete
         CVX_PH(4);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int row = tid + F32_T * h;
+            unsigned m = s_nzm[row];
+            if (__popc(m) > 4) {
+                s_dq[atomicAdd(&s_dqn, 1)] = (unsigned short)row;
+            } else {
+                const float* rp = sm + row * 32;
+                const int sw = (row & 7) << 2;
+                int at = s_base[row];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (m) {
+                        const int x = __ffs(m) - 1;
+                        m &= m - 1;
+                        s_list[at++] = make_uint2((unsigned)(row * 32 + x), __float_as_uint(rp[x ^ sw]));
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        for (int i = warp; i < s_dqn; i += F32_T / 32) {
+            const int rr = s_dq[i];
+            const unsigned mm = s_nzm[rr];
+            if ((mm >> lane) & 1u)
+                s_list[s_base[rr] + __popc(mm & lt)] = make_uint2((unsigned)(rr * 32 + lane), __float_as_uint(sm[rr * 32 + (lane ^ ((rr & 7) << 2))]));
+        }
+        __syncthreads();                 // list complete; nobody reads the block buffer any more
         if (tid == 0) {                  // the next block streams in while this one is coded
-            const unsigned int nt = atomicAdd(p.ticket, 1u);
             s_ticket[(it + 1) & 1] = nt;
             if (use_tma && nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
         }
-        {
-            const float T = nz_threshold(mulfac);
-#pragma unroll
-            for (int k = 0; k < 2; ++k)
-#pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const bool nz = !(fabsf(V_(k, r)) <= T);
-                    const unsigned m = __ballot_sync(0xffffffffu, nz);
-                    // unconditional (broadcast) load of the row base: 64 independent loads pipeline instead of
-                    // 64 dependent load->store chains inside divergent branches
-                    const int row = reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k;
-                    const int at = s_base[row] + __popc(m & lt);
-                    if (nz) s_list[at] = make_uint2((unsigned)(row * 32 + lane), __float_as_uint(V_(k, r)));
-                }
-        }
+        f32_mark_groups<F32_T>(s_list, n, mulfac);
         __syncthreads();
         CVX_PH(5);
-        // ---- tokens per list entry: thread = contiguous chunk of entries ----
-        const int per = (n + F32_T - 1) / F32_T;
-        const int e0 = min(n, tid * per), e1 = min(n, e0 + per);
-        int bytes = 0;
-        {
-            int prev = e0 > 0 ? (int)s_list[e0 - 1].x : -1;
-            for (int e = e0; e < e1; ++e) {
-                const EntryTok k = entry_token(s_list, n, e, prev, mulfac);
-                bytes += k.bytes;
-                prev = (int)s_list[e].x;
+        // ---- tokens per list entry: chunks of 32 consecutive entries are dealt round-robin to the warps (the dense
+        //      head of a block -- group-of-8 candidates, wide values -- is spread over all of them); byte offsets by a
+        //      shuffle scan inside the chunk + one scan of the (<= 128) chunk totals ----
+        const int nchunks = (n + 31) >> 5;
+        for (int c = warp; c < nchunks; c += F32_T / 32) {
+            const int e = 32 * c + lane;
+            int bytes = 0;
+            uint2 ent = make_uint2(0u, 0u);
+            if (e < n) {
+                ent = s_list[e];
+                const int prev = e > 0 ? (int)(s_list[e - 1].x & F32_IDX_MASK) : -1;
+                bytes = entry_token(ent, prev, mulfac).bytes;
             }
+            int incl = bytes;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += y;
+            }
+            // park the entry's offset inside its chunk next to the index (read back by the emit pass)
+            if (e < n) s_list[e].x = ent.x | ((unsigned)(incl - bytes) << 15);
+            if (lane == 31) s_chunk[c] = incl;
         }
+        __syncthreads();
         int len;
-        int pos = cta_excl_sum<F32_T>(bytes, scratch, len);
+        int cpre[4];                     // lane l: exclusive byte offsets of chunks 4l .. 4l+3 (every warp computes all of them)
+        {
+            int cs[4], tot = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { cs[i] = (4 * lane + i < nchunks) ? s_chunk[4 * lane + i] : 0; tot += cs[i]; }
+            int sc = tot;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, sc, d);
+                if (lane >= d) sc += y;
+            }
+            len = __shfl_sync(0xffffffffu, sc, 31);
+            cpre[0] = sc - tot;
+#pragma unroll
+            for (int i = 1; i < 4; ++i) cpre[i] = cpre[i - 1] + cs[i - 1];
+        }
         CVX_PH(6);
-        const int tail_run = F32_B - 1 - (n > 0 ? (int)s_list[n - 1].x : -1);      // final flush (:294)
+        const int tail_run = F32_B - 1 - (n > 0 ? (int)(s_list[n - 1].x & F32_IDX_MASK) : -1);      // final flush (:294)
         const int tail_pos = len;
         len += run_bytes(tail_run);
         if (tid == 0) publish_aggregate(p, t, (unsigned long long)len);
@@ -254,11 +303,18 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
         unsigned char* out = direct ? p.payload + excl_now : s_stage + buf * F32_STAGE;
         if (fits) {
             auto put = [&](int ps, uint8_t b) { out[ps] = b; };
-            int prev = e0 > 0 ? (int)s_list[e0 - 1].x : -1;
-            for (int e = e0; e < e1; ++e) {
-                const EntryTok k = entry_token(s_list, n, e, prev, mulfac);
-                prev = (int)s_list[e].x;
+            for (int c = warp; c < nchunks; c += F32_T / 32) {
+                const int src = c >> 2;
+                const int b0 = __shfl_sync(0xffffffffu, cpre[0], src), b1 = __shfl_sync(0xffffffffu, cpre[1], src);
+                const int b2 = __shfl_sync(0xffffffffu, cpre[2], src), b3 = __shfl_sync(0xffffffffu, cpre[3], src);
+                const int cbase = (c & 2) ? ((c & 1) ? b3 : b2) : ((c & 1) ? b1 : b0);
+                const int e = 32 * c + lane;
+                if (e >= n) continue;
+                const uint2 ent = s_list[e];
+                const int prev = e > 0 ? (int)(s_list[e - 1].x & F32_IDX_MASK) : -1;
+                const EntryTok k = entry_token(ent, prev, mulfac);
                 if (k.bytes == 0) continue;
+                int pos = cbase + (int)((ent.x >> 15) & F32_OFF_MASK);
                 pos = put_run(k.run, pos, put);
                 if (k.mode == GM_ELEM) {
                     pos = put_elem(k.q, k.f, pos, put);

@@ -208,9 +208,13 @@ __device__ __forceinline__ float nz_threshold(float m)
     return t;
 }
 
-// One entry of the sorted non-zero list.  Returns the bytes it emits (its zero-run flush included) and, through
-// `mode`/`lead`, whether it belongs to an aligned group of 8 non-zeros coded as one VLESC2_8x / VLESC3_8x token
-// (Run_Length_Encode_Slow.cpp:231-256); such a group is written by its first entry alone.
+// One entry of the sorted non-zero list: list[e].y = coefficient bits, list[e].x =
+//   bits  0..14  raster index
+//   bits 15..24  byte offset of the entry inside its chunk of 32 entries (parked by the sizing pass)
+//   bits 30..31  group flag: 0 plain, 1 member of an 8-value token (written by its leader), 2 leader of a VLESC2_8x
+//                group, 3 leader of a VLESC3_8x group (Run_Length_Encode_Slow.cpp:231-256), set by f32_mark_groups
+constexpr unsigned F32_IDX_MASK = 0x7FFFu;
+constexpr unsigned F32_OFF_MASK = 0x3FFu;
 struct EntryTok {
     int run;        // zeros between the previous non-zero and this one
     int q;          // quantised value
@@ -218,25 +222,39 @@ struct EntryTok {
     int mode;       // GM_ELEM, GM_S8, GM_T8
     int bytes;      // bytes this entry is responsible for
 };
-__device__ __forceinline__ EntryTok entry_token(const uint2* list, int n, int e, int prev_idx, float mulfac)
+__device__ __forceinline__ EntryTok entry_token(uint2 ent, int prev_idx, float mulfac)
 {
     EntryTok k;
-    const uint2 ent = list[e];
-    const int idx = (int)ent.x;
+    const int idx = (int)(ent.x & F32_IDX_MASK);
+    const unsigned flag = ent.x >> 30;
     k.run = idx - prev_idx - 1;
     k.f = __fmul_rn(mulfac, __uint_as_float(ent.y));
     k.q = quantise(k.f);
-    k.mode = GM_ELEM;
-    const int j = idx & 7, le = e - j;
-    if (le >= 0 && le + 7 < n && (int)list[le].x == idx - j && (int)list[le + 7].x == idx - j + 7) {
+    k.mode = flag == 2u ? GM_S8 : flag == 3u ? GM_T8 : GM_ELEM;
+    if (flag == 0u) k.bytes = run_bytes(k.run) + elem_bytes(k.q);
+    else if (flag == 1u) k.bytes = 0;
+    else k.bytes = run_bytes(k.run) + (flag == 2u ? 17 : 25);
+    return k;
+}
+
+// Aligned groups of 8 consecutive non-zeros that the reference codes as one 8-value token: the group's first entry
+// decides (group_mode) and flags all eight.  Entry e is examined by thread e mod T.
+template <int T>
+__device__ __forceinline__ void f32_mark_groups(uint2* list, int n, float mulfac)
+{
+    for (int e = threadIdx.x; e + 7 < n; e += T) {
+        const int idx = (int)(list[e].x & F32_IDX_MASK);
+        if ((idx & 7) != 0 || (int)(list[e + 7].x & F32_IDX_MASK) != idx + 7) continue;
         int q8[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) q8[i] = quantise(__fmul_rn(mulfac, __uint_as_float(list[le + i].y)));
-        k.mode = group_mode(q8);
+        for (int i = 0; i < 8; ++i) q8[i] = quantise(__fmul_rn(mulfac, __uint_as_float(list[e + i].y)));
+        const int mode = group_mode(q8);
+        if (mode == GM_S8 || mode == GM_T8) {
+            list[e].x |= (mode == GM_S8 ? 2u : 3u) << 30;
+#pragma unroll
+            for (int i = 1; i < 8; ++i) list[e + i].x |= 1u << 30;
+        }
     }
-    if (k.mode == GM_ELEM) k.bytes = run_bytes(k.run) + elem_bytes(k.q);
-    else k.bytes = j == 0 ? run_bytes(k.run) + (k.mode == GM_S8 ? 17 : 25) : 0;
-    return k;
 }
 
 template <class Put>
