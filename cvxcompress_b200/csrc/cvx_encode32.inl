@@ -315,10 +315,10 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
                 const EntryTok k = entry_token(ent, prev, mulfac);
                 if (k.bytes == 0) continue;
                 int pos = cbase + (int)((ent.x >> 15) & F32_OFF_MASK);
-                pos = put_run(k.run, pos, put);
                 if (k.mode == GM_ELEM) {
-                    pos = put_elem(k.q, k.f, pos, put);
+                    put_entry_branchfree(out, pos, k.run, k.q, k.f);
                 } else {
+                    pos = put_run(k.run, pos, put);
                     const int w = k.mode == GM_S8 ? 2 : 3;
                     put(pos++, (uint8_t)(k.mode == GM_S8 ? VLESC2_8x : VLESC3_8x));
                     for (int i = 0; i < 8; ++i) {

@@ -213,6 +213,7 @@ __device__ __forceinline__ float nz_threshold(float m)
 //   bits 15..24  byte offset of the entry inside its chunk of 32 entries (parked by the sizing pass)
 //   bits 30..31  group flag: 0 plain, 1 member of an 8-value token (written by its leader), 2 leader of a VLESC2_8x
 //                group, 3 leader of a VLESC3_8x group (Run_Length_Encode_Slow.cpp:231-256), set by f32_mark_groups
+__device__ __forceinline__ int run_bytes_small(int r) { return r <= 0 ? 0 : r == 1 ? 1 : r < 256 ? 2 : 4; }   // runs < 2^24
 constexpr unsigned F32_IDX_MASK = 0x7FFFu;
 constexpr unsigned F32_OFF_MASK = 0x3FFu;
 struct EntryTok {
@@ -231,9 +232,9 @@ __device__ __forceinline__ EntryTok entry_token(uint2 ent, int prev_idx, float m
     k.f = __fmul_rn(mulfac, __uint_as_float(ent.y));
     k.q = quantise(k.f);
     k.mode = flag == 2u ? GM_S8 : flag == 3u ? GM_T8 : GM_ELEM;
-    if (flag == 0u) k.bytes = run_bytes(k.run) + elem_bytes(k.q);
+    if (flag == 0u) k.bytes = run_bytes_small(k.run) + elem_bytes(k.q);
     else if (flag == 1u) k.bytes = 0;
-    else k.bytes = run_bytes(k.run) + (flag == 2u ? 17 : 25);
+    else k.bytes = run_bytes_small(k.run) + (flag == 2u ? 17 : 25);
     return k;
 }
 
@@ -271,6 +272,29 @@ __device__ __forceinline__ int put_elem(int v, float f, int pos, Put put)
     put(pos, (uint8_t)VLESC4); put(pos + 1, (uint8_t)(u & 0xFF)); put(pos + 2, (uint8_t)((u >> 8) & 0xFF));
     put(pos + 3, (uint8_t)((u >> 16) & 0xFF)); put(pos + 4, (uint8_t)(u >> 24));
     return pos + 5;
+}
+
+// Branch-free emission of one element-mode entry (zero-run flush + value token, Run_Length_Encode_Slow.cpp:21-71 and
+// :161-174) for runs below 2^24 (a 32^3 block has 2^15 cells): both tokens are composed with selects and written with
+// predicated byte stores, so a warp whose lanes hold different token kinds does not serialise.
+__device__ __forceinline__ void put_entry_branchfree(unsigned char* out, int pos, int run, int q, float f)
+{
+    // run token: none | 00 | 7F r | 7D r0 r1 r2
+    const int rl = run_bytes_small(run);
+    const unsigned rv = run == 1 ? 0u : run < 256 ? (0x7Fu | ((unsigned)run << 8)) : (0x7Du | ((unsigned)run << 8));
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i < rl) out[pos + i] = (unsigned char)(rv >> (8 * i));
+    pos += rl;
+    // value token: q | 83 q0 q1 | 81 q0 q1 q2 | 80 f0 f1 f2 f3
+    const bool b = is_b(q), s2 = is_s(q), s3 = is_3(q);
+    const int el = b ? 1 : s2 ? 3 : s3 ? 4 : 5;
+    const unsigned code = b ? (unsigned)(q & 0xFF) : s2 ? (unsigned)(VLESC2 & 0xFF) : s3 ? (unsigned)(VLESC3 & 0xFF) : (unsigned)(VLESC4 & 0xFF);
+    const unsigned pay = (s2 || s3) ? (unsigned)q : __float_as_uint(f);
+    out[pos] = (unsigned char)code;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i + 1 < el) out[pos + 1 + i] = (unsigned char)(pay >> (8 * i));
 }
 
 // staged payload (shared memory, 16-byte aligned) -> global, any destination alignment: 32-bit coalesced stores
