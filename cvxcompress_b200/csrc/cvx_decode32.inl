@@ -111,27 +111,32 @@ __device__ __forceinline__ int d32_nchunks(int entry, long hint)
 // chunks before it, then the chunk itself with value counting.  Straight-line code (selects, clamped loads, no
 // branches) so that the compiler can interleave it with the packed z-line arithmetic of the PREVIOUS block, whose
 // FFMA2/FADD2 stream leaves half of the issue slots free.
+__device__ __forceinline__ void d32_walk_one(const uint64_t* w64, int entry, int nch, int j, D32Walk& w)
+{
+    const int c = threadIdx.x + D32_T * j;
+    const bool act = c < nch;
+    const uint64_t P2 = w64[c >= 2 ? c - 2 : 0], P1 = w64[c >= 1 ? c - 1 : 0];
+    w.A[j] = w64[c]; w.N[j] = w64[c + 1];
+    int d = 0, dummy = 0;
+    chunk8_walk<false>(P2, 0ull, d, dummy);
+    d = (c == 1) ? entry : d;             // chunk 1: exact entry through chunk 0
+    chunk8_walk<false>(P1, 0ull, d, dummy);
+    d = (c == 0) ? entry : d;
+    w.ent[j] = d;
+    int cnt = 0;
+    const uint32_t m = chunk8_walk<true>(w.A[j], w.N[j], d, cnt);
+    w.mask[j] = act ? m : 0u;
+    w.cnt[j] = act ? cnt : 0;
+    w.ext[j] = act ? d : 0;
+}
 __device__ __forceinline__ void d32_walk(const unsigned char* win, int entry, int nch, D32Walk& w)
 {
     const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int c = threadIdx.x + D32_T * j;
-        const bool act = c < nch;
-        const uint64_t P2 = w64[c >= 2 ? c - 2 : 0], P1 = w64[c >= 1 ? c - 1 : 0];
-        w.A[j] = w64[c]; w.N[j] = w64[c + 1];
-        int d = 0, dummy = 0;
-        chunk8_walk<false>(P2, 0ull, d, dummy);
-        d = (c == 1) ? entry : d;         // chunk 1: exact entry through chunk 0
-        chunk8_walk<false>(P1, 0ull, d, dummy);
-        d = (c == 0) ? entry : d;
-        w.ent[j] = d;
-        int cnt = 0;
-        const uint32_t m = chunk8_walk<true>(w.A[j], w.N[j], d, cnt);
-        w.mask[j] = act ? m : 0u;
-        w.cnt[j] = act ? cnt : 0;
-        w.ext[j] = act ? d : 0;
-    }
+    // chunks 512..1023 only exist for payloads above 4 KiB (or an unknown length): CTA-uniform branch, placed first so
+    // that the always-executed half below stays in one basic block with the arithmetic that follows the call
+    w.A[1] = 0; w.N[1] = 0; w.mask[1] = 0; w.cnt[1] = 0; w.ext[1] = 0; w.ent[1] = 0;
+    if (nch > D32_T) d32_walk_one(w64, entry, nch, 1, w);
+    d32_walk_one(w64, entry, nch, 0, w);
 }
 
 // parse the block whose first window is staged in `win` and already walked (`w`); writes coefficients through put(i, v)
