@@ -91,32 +91,38 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 template <bool EXACT, bool FWD>
 __device__ __forceinline__ void f32_pass_x(float* sm)
 {
-#pragma unroll 1
-    for (int r = threadIdx.x; r < F32_ROWS; r += F32_T) {
-        float4* row = reinterpret_cast<float4*>(sm + r * 32);
-        const int k = r & 7;
-        float v[32];
-        if (FWD) {
+    // both rows of the thread (r = tid and tid + 512) in one straight-line block: the two independent dependency
+    // chains interleave and fill the FMA pipe where one row's deep (short) levels would leave bubbles
+    float4* row0 = reinterpret_cast<float4*>(sm + threadIdx.x * 32);
+    float4* row1 = row0 + (F32_T * 32) / 4;
+    const int k = threadIdx.x & 7;                 // (tid + 512) & 7 == tid & 7: same swizzle for both rows
+    float v[2][32];
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                float4 q = row[c ^ k];
-                v[4 * c] = q.x; v[4 * c + 1] = q.y; v[4 * c + 2] = q.z; v[4 * c + 3] = q.w;
+    for (int h = 0; h < 2; ++h) {
+        float4* row = h ? row1 : row0;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            float4 q = row[c ^ k];
+            if (FWD) {
+                v[h][4 * c] = q.x; v[h][4 * c + 1] = q.y; v[h][4 * c + 2] = q.z; v[h][4 * c + 3] = q.w;
+            } else {
+                v[h][sub_to_reg<32, EXACT>(4 * c)] = q.x; v[h][sub_to_reg<32, EXACT>(4 * c + 1)] = q.y;
+                v[h][sub_to_reg<32, EXACT>(4 * c + 2)] = q.z; v[h][sub_to_reg<32, EXACT>(4 * c + 3)] = q.w;
             }
-            fwd_line<32, EXACT>(v);
+        }
+    }
+    if (FWD) { fwd_line<32, EXACT>(v[0]); fwd_line<32, EXACT>(v[1]); }
+    else { inv_line<32, EXACT>(v[0]); inv_line<32, EXACT>(v[1]); }
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-                row[c ^ k] = make_float4(v[sub_to_reg<32, EXACT>(4 * c)], v[sub_to_reg<32, EXACT>(4 * c + 1)],
-                                         v[sub_to_reg<32, EXACT>(4 * c + 2)], v[sub_to_reg<32, EXACT>(4 * c + 3)]);
-        } else {
+    for (int h = 0; h < 2; ++h) {
+        float4* row = h ? row1 : row0;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                float4 q = row[c ^ k];
-                v[sub_to_reg<32, EXACT>(4 * c)] = q.x; v[sub_to_reg<32, EXACT>(4 * c + 1)] = q.y;
-                v[sub_to_reg<32, EXACT>(4 * c + 2)] = q.z; v[sub_to_reg<32, EXACT>(4 * c + 3)] = q.w;
-            }
-            inv_line<32, EXACT>(v);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) row[c ^ k] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+        for (int c = 0; c < 8; ++c) {
+            if (FWD)
+                row[c ^ k] = make_float4(v[h][sub_to_reg<32, EXACT>(4 * c)], v[h][sub_to_reg<32, EXACT>(4 * c + 1)],
+                                         v[h][sub_to_reg<32, EXACT>(4 * c + 2)], v[h][sub_to_reg<32, EXACT>(4 * c + 3)]);
+            else
+                row[c ^ k] = make_float4(v[h][4 * c], v[h][4 * c + 1], v[h][4 * c + 2], v[h][4 * c + 3]);
         }
     }
 }
