@@ -317,3 +317,71 @@ def test_full_size_config3_golden_length_and_roundtrip(gpu):
     assert ln2 == ln and torch.equal(s[:ln - 7], s2[:ln - 7])          # deterministic, natural block order
     offs = s[32:32 + 8 * 38610].view(torch.int64)
     assert bool((offs[1:] > offs[:-1]).all())                          # sorted offsets == natural order
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("case", [("g2", 96, 64, 160, 32, 32, 32, 1e-2, False), ("g2", 70, 50, 100, 16, 16, 16, 1e-3, True)],
+                         ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g-l%d" % c)
+def test_sharded_pieces_on_one_gpu(gpu, world, case):
+    """SURVEY.md 8(e) through the C-ABI pieces (cvxgpu_sumsq_device / encode_blocks / offsets / decode_blocks) with the
+    ranks of a `world`-GPU job run one after the other on this GPU: the assembled stream equals the oracle's."""
+    import torch
+    from cvxcompress_b200 import sharded
+    kind, nx, ny, nz, bx, by, bz, scale, local = case
+    vol = _vol(kind, nx, ny, nz)
+    be = sharded.CudaBackend()
+    geoms = [sharded.Geometry(nx, ny, nz, bx, by, bz, r, world) for r in range(world)]
+    slabs = [torch.from_numpy(np.ascontiguousarray(vol[g.z0:g.z1])).cuda() for g in geoms]
+    # (1) per-rank sums of squares, added in rank order (what the all-gather + fixed-order sum does)
+    total = torch.zeros(1, dtype=torch.float64, device="cuda")
+    if not local:
+        for s in slabs:
+            total += be.sumsq(s)
+    header = be.header(geoms[0], scale, local, total).cpu().numpy()
+    # (2) per-rank encode, (3) bases from the payload sizes
+    parts, base = [], 0
+    for g, s in zip(geoms, slabs):
+        n = g.nblk_slab
+        offs = torch.zeros(max(n, 1), dtype=torch.int64, device="cuda")
+        bmf = torch.zeros(max(n, 1), dtype=torch.float32, device="cuda") if local else None
+        pay = torch.zeros(4 * s.numel() + 4096, dtype=torch.uint8, device="cuda")
+        nb = torch.zeros(1, dtype=torch.int64, device="cuda")
+        st = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if n:
+            be.encode_blocks(s, g, scale, local, total, offs, bmf, pay, nb, st)
+        assert int(st.item()) == 0
+        nbytes = int(nb.item())
+        parts.append((g, offs[:n], bmf[:n] if local else None, pay, nbytes, base))
+        base += nbytes
+    g0 = geoms[0]
+    tb = g0.table_bytes(local)
+    full = np.zeros(32 + tb + base + 7, np.uint8)
+    full[:32] = header
+    tab = full[32:32 + 8 * g0.nblk].view(np.int64)
+    mf = full[32 + 8 * g0.nblk:32 + 12 * g0.nblk].view(np.float32) if local else None
+    for g, offs, bmf, pay, nbytes, b in parts:
+        tab[g.blk_first:g.blk_first + g.nblk_slab] = (offs + b).cpu().numpy()        # int64 add keeps the raw flag (bit 63)
+        if local:
+            mf[g.blk_first:g.blk_first + g.nblk_slab] = bmf.cpu().numpy()
+        full[32 + tb + b:32 + tb + b + nbytes] = pay[:nbytes].cpu().numpy()
+    want, _ = ol.oracle_compress(vol, bx, by, bz, scale, local)
+    assert _streams_equal(full, want)
+    # every rank decodes its slab from its own shard
+    ref = ol.oracle_decompress(want, nx, ny, nz)
+    gm = float(np.frombuffer(full[24:28].tobytes(), np.float32)[0])
+    for g, offs, bmf, pay, nbytes, b in parts:
+        out = torch.zeros((g.nz_slab, ny, nx), dtype=torch.float32, device="cuda")
+        if g.nblk_slab:
+            be.decode_blocks(out, g, gm, local, offs, bmf, pay, nbytes)
+        assert np.array_equal(out.cpu().numpy().view(np.uint32), ref[g.z0:g.z1].view(np.uint32))
+
+
+def test_run_module_tests(gpu):
+    """CvxCompress::Run_Module_Tests (CvxCompress.hxx:133) of the GPU library: device-side property checks."""
+    from cvxcompress_b200 import _lib
+    L = _lib.lib()
+    fn = getattr(L, "_ZN11CvxCompress16Run_Module_TestsEbb")
+    fn.restype = C.c_bool
+    fn.argtypes = [C.c_void_p, C.c_bool, C.c_bool]
+    this = (C.c_char * 64)()                 # the class has no data members beyond its vptr, which the method does not use
+    assert fn(C.addressof(this), False, False)
