@@ -30,7 +30,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // stage the window [cbase, cbase + D32_WIN) (cbase 16-byte aligned); bytes at or beyond `hi` read as zero
 __device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi)
 {
-    for (int g = threadIdx.x; g < D32_WIN / 16; g += D32_T) {
+    for (int g = threadIdx.x; g < D32_WIN / 16; g += blockDim.x) {
         const uint8_t* a = cbase + 16 * g;
         long left = hi - a;
         int n = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
@@ -40,6 +40,7 @@ __device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8
 }
 
 // exclusive sum of a pair of 32-bit counts packed in 64 bits (each count <= 2^20, 512 threads: no carry between halves)
+template <int T>
 __device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long v, unsigned long long* scratch64, unsigned long long& total)
 {
     unsigned long long x = v;
@@ -50,14 +51,14 @@ __device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long 
     }
     if (lane_id() == 31) scratch64[warp_id()] = x;
     __syncthreads();
-    unsigned long long w = lane_id() < D32_T / 32 ? scratch64[lane_id()] : 0ull;
+    unsigned long long w = lane_id() < T / 32 ? scratch64[lane_id()] : 0ull;
     unsigned long long s = w;
 #pragma unroll
-    for (int d = 1; d < 16; d <<= 1) {
+    for (int d = 1; d < T / 32; d <<= 1) {
         unsigned long long y = __shfl_up_sync(0xffffffffu, s, d);
         if (lane_id() >= d) s += y;
     }
-    total = __shfl_sync(0xffffffffu, s, D32_T / 32 - 1);
+    total = __shfl_sync(0xffffffffu, s, T / 32 - 1);
     const unsigned long long wbase = __shfl_sync(0xffffffffu, s - w, warp_id());
     __syncthreads();
     return wbase + x - v;
@@ -111,9 +112,10 @@ __device__ __forceinline__ int d32_nchunks(int entry, long hint)
 // chunks before it, then the chunk itself with value counting.  Straight-line code (selects, clamped loads, no
 // branches) so that the compiler can interleave it with the packed z-line arithmetic of the PREVIOUS block, whose
 // FFMA2/FADD2 stream leaves half of the issue slots free.
+template <int T>
 __device__ __forceinline__ void d32_walk_one(const uint64_t* w64, int entry, int nch, int j, D32Walk& w)
 {
-    const int c = threadIdx.x + D32_T * j;
+    const int c = threadIdx.x + T * j;
     const bool act = c < nch;
     const uint64_t P2 = w64[c >= 2 ? c - 2 : 0], P1 = w64[c >= 1 ? c - 1 : 0];
     w.A[j] = w64[c]; w.N[j] = w64[c + 1];
@@ -129,18 +131,19 @@ __device__ __forceinline__ void d32_walk_one(const uint64_t* w64, int entry, int
     w.cnt[j] = act ? cnt : 0;
     w.ext[j] = act ? d : 0;
 }
+template <int T>
 __device__ __forceinline__ void d32_walk(const unsigned char* win, int entry, int nch, D32Walk& w)
 {
     const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
     // chunks 512..1023 only exist for payloads above 4 KiB (or an unknown length): CTA-uniform branch, placed first so
     // that the always-executed half below stays in one basic block with the arithmetic that follows the call
     w.A[1] = 0; w.N[1] = 0; w.mask[1] = 0; w.cnt[1] = 0; w.ext[1] = 0; w.ent[1] = 0;
-    if (nch > D32_T) d32_walk_one(w64, entry, nch, 1, w);
-    d32_walk_one(w64, entry, nch, 0, w);
+    if constexpr (T < D32_CH) { if (nch > T) d32_walk_one<T>(w64, entry, nch, 1, w); }
+    d32_walk_one<T>(w64, entry, nch, 0, w);
 }
 
 // parse the block whose first window is staged in `win` and already walked (`w`); writes coefficients through put(i, v)
-template <class PutV>
+template <int T, class PutV>
 __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, unsigned char* win, int* s_ext,
                                           unsigned long long* scratch64, D32Walk& w, PutV put)
 {
@@ -157,17 +160,17 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
             d32_issue_window(win, cbase, hi);
             cp_async_wait_all();
             __syncthreads();
-            d32_walk(win, entry, nch, w);
+            d32_walk<T>(win, entry, nch, w);
         }
         for (;;) {                        // verify exit(c-1) == entry(c); repair until the chain is consistent
 #pragma unroll
-            for (int j = 0; j < 2; ++j) { const int c = tid + D32_T * j; if (c < nch) s_ext[c] = w.ext[j]; }
+            for (int j = 0; j < 2; ++j) { const int c = tid + T * j; if (c < nch) s_ext[c] = w.ext[j]; }
             __syncthreads();
             bool bad[2];
             int want[2];
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
-                const int c = tid + D32_T * j;
+                const int c = tid + T * j;
                 want[j] = (c > 0 && c < nch) ? s_ext[c - 1] : w.ent[j];
                 bad[j] = want[j] != w.ent[j];
             }
@@ -184,12 +187,12 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
         }
         const unsigned c0 = (unsigned)min(w.cnt[0], 1 << 20), c1 = (unsigned)min(w.cnt[1], 1 << 20);
         unsigned long long total;
-        const unsigned long long ex = d32_excl_sum64((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
+        const unsigned long long ex = d32_excl_sum64<T>((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
         const long tot0 = (long)(total & 0xFFFFFFFFull), tot1 = (long)(total >> 32);
         long vi0 = (long)produced + (long)(ex & 0xFFFFFFFFull);
         long vi1 = (long)produced + tot0 + (long)(ex >> 32);
         if (w.mask[0] && vi0 < F32_B) chunk8_expand(w.mask[0], w.A[0], w.N[0], 8 * tid, (int)vi0, F32_B, b.scalefac, getb, put);
-        if (w.mask[1] && vi1 < F32_B) chunk8_expand(w.mask[1], w.A[1], w.N[1], 8 * (tid + D32_T), (int)vi1, F32_B, b.scalefac, getb, put);
+        if (w.mask[1] && vi1 < F32_B) chunk8_expand(w.mask[1], w.A[1], w.N[1], 8 * (tid + T), (int)vi1, F32_B, b.scalefac, getb, put);
         long np = (long)produced + tot0 + tot1;
         produced = np > (1 << 30) ? (1 << 30) : (int)np;
         if (produced >= F32_B) break;
@@ -199,14 +202,15 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
     }
 }
 
-template <bool EXACT>
-__global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
+template <bool EXACT, int T>
+__global__ void __launch_bounds__(T, 1) k_decode32(const DecParams p)
 {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     unsigned char* s_win = smem_raw + D32_OFF_WIN;
     int* s_ext = reinterpret_cast<int*>(smem_raw + D32_OFF_EXT);
-    __shared__ unsigned long long scratch64[D32_T / 32];
+    __shared__ unsigned long long scratch64[T / 32];
+    constexpr int LPT = 1024 / T;                                   // z lines (and x rows, y lines) per thread
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint8_t* hi = p.payload + p.payload_bytes;
@@ -220,14 +224,14 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
     {
         float4* z4 = reinterpret_cast<float4*>(sm);
 #pragma unroll
-        for (int i = 0; i < F32_B / 4 / D32_T; ++i) z4[tid + D32_T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < F32_B / 4 / T; ++i) z4[tid + T * i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     D32Walk wk;
     cp_async_wait_all();
     __syncthreads();                                                // first window staged, block buffer zeroed
     {
         const int entry = (int)(reinterpret_cast<uintptr_t>(cur.src) & 15);
-        d32_walk(s_win, entry, d32_nchunks(entry, cur.hint), wk);
+        d32_walk<T>(s_win, entry, d32_nchunks(entry, cur.hint), wk);
     }
     CVX_PH_DECL;
     for (;;) {
@@ -237,7 +241,7 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
         CVX_PH(0);
         if (cur.raw) {                                              // CvxCompress.cpp:555: B fp32 coefficients
             __syncthreads();                                        // every thread has zeroed its cells of the previous block
-            for (int i = tid; i < F32_B; i += D32_T) {
+            for (int i = tid; i < F32_B; i += T) {
                 uint32_t u = 0;
                 const uint8_t* s = cur.src + 4L * i;
                 if ((reinterpret_cast<uintptr_t>(cur.src) & 3) == 0 && s + 4 <= hi) u = *reinterpret_cast<const uint32_t*>(s);
@@ -245,7 +249,7 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                 sm[physr(i, 5)] = __uint_as_float(u);
             }
         } else {
-            d32_parse(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
+            d32_parse<T>(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
         }
         __syncthreads();
         CVX_PH(1);
@@ -254,14 +258,14 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                              reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi);
         // warp w owns the x rows AND the y lines of the z slices w and w + 16: no CTA barrier between the two passes,
         // so warps drift apart and one warp's shared-memory traffic overlaps another's arithmetic
-        f32_pass_x<EXACT, false>(sm);
+        f32_pass_xT<EXACT, false, T>(sm);
         __syncwarp();
         CVX_PH(2);
-        f32_pass_y2<EXACT, false>(sm);
+        f32_pass_yT<EXACT, false, T>(sm);
         cp_async_wait_all();                                        // this thread's part of the next window has landed ...
         __syncthreads();                                            // ... and everybody's; all y lines are written
         CVX_PH(3);
-        typename PairOf<EXACT>::type v[32];                         // z lines (x = lane, y = warp) and (x, y + 16), packed
+        typename LineOf<EXACT, T>::type v[32];                      // z line(s): (x = lane, y = warp) [and (x, y + 16), packed]
         {
             // each thread reads its two z lines and leaves zeros behind: the buffer is clean for the next block's
             // expansion without another barrier or a separate fill pass
@@ -272,7 +276,7 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
                 p_set(v[r], e[0], e[512]);
             }
 #pragma unroll
-            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
+            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; if (LPT == 2) zl[r * 1024 + 512] = 0.f; }
         }
         CVX_PH(4);
         const int iix = (int)(t % p.nbx);
@@ -284,11 +288,11 @@ __global__ void __launch_bounds__(D32_T, 1) k_decode32(const DecParams p)
             // walk the NEXT block's chunks here: integer work that fills the issue slots the packed z-line arithmetic leaves
             // free (no branch in between, so both streams are scheduled together)
             const int entry = (int)(reinterpret_cast<uintptr_t>(nxt.src) & 15);
-            d32_walk(s_win + (buf ^ 1) * D32_WIN, entry, d32_nchunks(entry, nxt.hint), wk);
+            d32_walk<T>(s_win + (buf ^ 1) * D32_WIN, entry, d32_nchunks(entry, nxt.hint), wk);
         }
         inv_line<32, EXACT>(v);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < LPT; ++k) {
             const int gy = iiy * 32 + warp + 16 * k;
             if (gx < p.g.nx && gy < p.g.ny) {
                 float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;

@@ -190,6 +190,65 @@ __device__ __forceinline__ void f32_pass_y2(float* sm)
     }
 }
 
+// ---- thread-count generic passes: T = 512 (two lines per thread) or 1024 (one line per thread, 64-register budget,
+//      twice the warps to hide latencies; LIFTING only -- the EXACT level copy does not fit 64 registers) ----
+template <bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void f32_pass_xT(float* sm)
+{
+    if constexpr (T == 512) {
+        f32_pass_x<EXACT, FWD>(sm);
+    } else {
+        float4* row = reinterpret_cast<float4*>(sm + threadIdx.x * 32);
+        const int k = threadIdx.x & 7;
+        float v[32];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            float4 q = row[c ^ k];
+            if (FWD) {
+                v[4 * c] = q.x; v[4 * c + 1] = q.y; v[4 * c + 2] = q.z; v[4 * c + 3] = q.w;
+            } else {
+                v[sub_to_reg<32, EXACT>(4 * c)] = q.x; v[sub_to_reg<32, EXACT>(4 * c + 1)] = q.y;
+                v[sub_to_reg<32, EXACT>(4 * c + 2)] = q.z; v[sub_to_reg<32, EXACT>(4 * c + 3)] = q.w;
+            }
+        }
+        if (FWD) fwd_line<32, EXACT>(v); else inv_line<32, EXACT>(v);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            if (FWD)
+                row[c ^ k] = make_float4(v[sub_to_reg<32, EXACT>(4 * c)], v[sub_to_reg<32, EXACT>(4 * c + 1)],
+                                         v[sub_to_reg<32, EXACT>(4 * c + 2)], v[sub_to_reg<32, EXACT>(4 * c + 3)]);
+            else
+                row[c ^ k] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+        }
+    }
+}
+template <bool EXACT, bool FWD, int T>
+__device__ __forceinline__ void f32_pass_yT(float* sm)
+{
+    if constexpr (T == 512) {
+        f32_pass_y2<EXACT, FWD>(sm);
+    } else {
+        const int x = threadIdx.x & 31, z = threadIdx.x >> 5;
+        float* a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = sm + z * 1024 + (x ^ (k << 2));
+        float v[32];
+        if (FWD) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = a[j & 7][j * 32];
+            fwd_line<32, EXACT>(v);
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { const int s = reg_to_sub<32, EXACT>(r); a[s & 7][s * 32] = v[r]; }
+        } else {
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { const int s = reg_to_sub<32, EXACT>(r); v[r] = a[s & 7][s * 32]; }
+            inv_line<32, EXACT>(v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) a[j & 7][j * 32] = v[j];
+        }
+    }
+}
+
 // z line of thread-line l (x = l & 31, y = l >> 5): element j at j*1024 + y*32 + (x ^ ((y & 7) << 2))
 __device__ __forceinline__ float* f32_zline(float* sm, int l)
 {

@@ -178,6 +178,13 @@ CVX_HD float p_hi(F2 v) { return f2_hi(v); }
 CVX_HD float p_lo(S2 v) { return v.x; }
 CVX_HD float p_hi(S2 v) { return v.y; }
 
+// a thread's bundle of lines: two side by side (512-thread kernels: F2 packed or S2 scalar) or one (1024-thread kernels)
+template <bool EXACT, int T> struct LineOf { typedef typename PairOf<EXACT>::type type; };
+template <bool EXACT> struct LineOf<EXACT, 1024> { typedef float type; };
+CVX_HD void p_set(float& d, float x, float) { d = x; }
+CVX_HD float p_lo(float v) { return v; }
+CVX_HD float p_hi(float v) { return v; }
+
 // ------------------------------------------------------------------------------------------
 // EXACT, register-resident.  One level on v[0..N): low half then high half (out-of-place
 // semantics through the copy t[]).
