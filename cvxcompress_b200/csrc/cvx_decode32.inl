@@ -28,9 +28,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // stage the window [cbase, cbase + D32_WIN) (cbase 16-byte aligned); bytes at or beyond `hi` read as zero
-__device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi)
+__device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi, int nthreads)
 {
-    for (int g = threadIdx.x; g < D32_WIN / 16; g += blockDim.x) {
+    for (int g = threadIdx.x; g < D32_WIN / 16; g += nthreads) {
         const uint8_t* a = cbase + 16 * g;
         long left = hi - a;
         int n = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
@@ -39,18 +39,37 @@ __device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8
     cp_async_commit();
 }
 
+// barrier policies: the whole CTA, or a named barrier over a subset of its warps (warp-specialised kernel)
+struct CtaBar {
+    __device__ __forceinline__ static void sync() { __syncthreads(); }
+    __device__ __forceinline__ static int sync_or(int pred) { return __syncthreads_or(pred); }
+};
+template <int ID, int N>
+struct NamedBar {
+    __device__ __forceinline__ static void sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
+    __device__ __forceinline__ static int sync_or(int pred)
+    {
+        int r;
+        asm volatile("{\n.reg .pred p, q;\nsetp.ne.s32 q, %1, 0;\nbar.red.or.pred p, %2, %3, q;\nselp.s32 %0, 1, 0, p;\n}"
+                     : "=r"(r) : "r"(pred), "n"(ID), "n"(N) : "memory");
+        return r;
+    }
+};
+
 // exclusive sum of a pair of 32-bit counts packed in 64 bits (each count <= 2^20, 512 threads: no carry between halves)
-template <int T>
+template <int T, class Bar>
 __device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long v, unsigned long long* scratch64, unsigned long long& total)
 {
+    static_assert((T & (T - 1)) == 0, "group size is a power of two");
+    const int gw = warp_id() & (T / 32 - 1);          // warp index inside the group (groups start at multiples of T/32 warps)
     unsigned long long x = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
         if (lane_id() >= d) x += y;
     }
-    if (lane_id() == 31) scratch64[warp_id()] = x;
-    __syncthreads();
+    if (lane_id() == 31) scratch64[gw] = x;
+    Bar::sync();
     unsigned long long w = lane_id() < T / 32 ? scratch64[lane_id()] : 0ull;
     unsigned long long s = w;
 #pragma unroll
@@ -59,8 +78,8 @@ __device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long 
         if (lane_id() >= d) s += y;
     }
     total = __shfl_sync(0xffffffffu, s, T / 32 - 1);
-    const unsigned long long wbase = __shfl_sync(0xffffffffu, s - w, warp_id());
-    __syncthreads();
+    const unsigned long long wbase = __shfl_sync(0xffffffffu, s - w, gw);
+    Bar::sync();
     return wbase + x - v;
 }
 
@@ -143,7 +162,7 @@ __device__ __forceinline__ void d32_walk(const unsigned char* win, int entry, in
 }
 
 // parse the block whose first window is staged in `win` and already walked (`w`); writes coefficients through put(i, v)
-template <int T, class PutV>
+template <int T, class Bar, class PutV>
 __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, unsigned char* win, int* s_ext,
                                           unsigned long long* scratch64, D32Walk& w, PutV put)
 {
@@ -156,16 +175,16 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
     for (bool first = true;; first = false) {
         const int nch = d32_nchunks(entry, hint);
         if (!first) {                     // rare: payload longer than one window, or a wrong hint
-            __syncthreads();
-            d32_issue_window(win, cbase, hi);
+            Bar::sync();
+            d32_issue_window(win, cbase, hi, T);
             cp_async_wait_all();
-            __syncthreads();
+            Bar::sync();
             d32_walk<T>(win, entry, nch, w);
         }
         for (;;) {                        // verify exit(c-1) == entry(c); repair until the chain is consistent
 #pragma unroll
             for (int j = 0; j < 2; ++j) { const int c = tid + T * j; if (c < nch) s_ext[c] = w.ext[j]; }
-            __syncthreads();
+            Bar::sync();
             bool bad[2];
             int want[2];
 #pragma unroll
@@ -175,7 +194,7 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
                 bad[j] = want[j] != w.ent[j];
             }
             const int last_ext = s_ext[nch - 1];
-            const int any = __syncthreads_or((bad[0] || bad[1]) ? 1 : 0);
+            const int any = Bar::sync_or((bad[0] || bad[1]) ? 1 : 0);
 #ifdef CVX_PHASE_TIMING
             if (tid == 0) atomicAdd(&g_phase[1][10], 1ull);
             if (bad[0] || bad[1]) atomicAdd(&g_phase[1][11], 1ull);
@@ -187,7 +206,7 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
         }
         const unsigned c0 = (unsigned)min(w.cnt[0], 1 << 20), c1 = (unsigned)min(w.cnt[1], 1 << 20);
         unsigned long long total;
-        const unsigned long long ex = d32_excl_sum64<T>((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
+        const unsigned long long ex = d32_excl_sum64<T, Bar>((unsigned long long)c0 | ((unsigned long long)c1 << 32), scratch64, total);
         const long tot0 = (long)(total & 0xFFFFFFFFull), tot1 = (long)(total >> 32);
         long vi0 = (long)produced + (long)(ex & 0xFFFFFFFFull);
         long vi1 = (long)produced + tot0 + (long)(ex >> 32);
@@ -220,7 +239,7 @@ __global__ void __launch_bounds__(T, 1) k_decode32(const DecParams p)
     if (t >= p.nblk) return;
     D32Src cur = d32_locate(p, t);
     int buf = 0;
-    d32_issue_window(s_win, reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(cur.src) & ~(uintptr_t)15), hi);
+    d32_issue_window(s_win, reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(cur.src) & ~(uintptr_t)15), hi, T);
     {
         float4* z4 = reinterpret_cast<float4*>(sm);
 #pragma unroll
@@ -249,13 +268,13 @@ __global__ void __launch_bounds__(T, 1) k_decode32(const DecParams p)
                 sm[physr(i, 5)] = __uint_as_float(u);
             }
         } else {
-            d32_parse<T>(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
+            d32_parse<T, CtaBar>(hi, cur, s_win + buf * D32_WIN, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
         }
         __syncthreads();
         CVX_PH(1);
         if (tn < p.nblk)                                            // next block's payload streams in under the transform
             d32_issue_window(s_win + (buf ^ 1) * D32_WIN,
-                             reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi);
+                             reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(nxt.src) & ~(uintptr_t)15), hi, T);
         // warp w owns the x rows AND the y lines of the z slices w and w + 16: no CTA barrier between the two passes,
         // so warps drift apart and one warp's shared-memory traffic overlaps another's arithmetic
         f32_pass_xT<EXACT, false, T>(sm);

@@ -1,0 +1,299 @@
+// cvx_decode32ws.inl -- k_decode32ws: warp-specialised 32^3 decoder (LIFTING arithmetic), included after cvx_decode32.inl.
+//
+// The fused decoder's phases each saturate ONE pipe -- the token parse the (half-rate) integer pipe, the line
+// transforms the FMA pipe, the row stores the load/store unit -- and in k_decode32 they run one after the other.
+// Here a CTA has 20 warps: warps 0..15 (the transform group) run expand -> x -> y -> z -> store of block t while
+// warps 16..19 (the parser group) turn block t+1's payload into a compact (raster index, value) list, so the
+// integer work of one block overlaps the floating-point work of its predecessor.
+//   parser:    payload window (cp.async) -> contiguous chunk ranges per thread (speculation only at the range start,
+//              exact state inside it) -> chain check over 128 threads -> value / entry counts -> scan -> list
+//   transform: scatter the list into its zeroed block buffer, then exactly the k_decode32 pipeline
+// Hand-over by two named barriers (FULL: list ready, EMPTY: list consumed).  A block the parser cannot serve (raw,
+// unknown payload length = foreign block order, payload or list larger than the staging) is flagged and decoded
+// in line by the transform group with the k_decode32 routines on a named barrier.
+
+constexpr int W32_TT = 512;                          // transform threads (warps 0..15)
+constexpr int W32_PT = 128;                          // parser threads (warps 16..19)
+constexpr int W32_T = W32_TT + W32_PT;
+constexpr int W32_LCAP = 6144;                       // list entries (8 bytes each)
+constexpr int W32_OFF_WIN = F32_B * 4;               // parser window, then the in-line window
+constexpr int W32_OFF_EXT = W32_OFF_WIN + 2 * D32_WIN;
+constexpr int W32_OFF_MASK = W32_OFF_EXT + D32_CH * 4;          // uint8[1024] token-start masks of the parser
+constexpr int W32_OFF_LIST = W32_OFF_MASK + D32_CH;
+constexpr int W32_SMEM = W32_OFF_LIST + W32_LCAP * 8;           // 201 824 bytes
+
+typedef NamedBar<1, W32_TT> TBar;                    // transform group
+typedef NamedBar<2, W32_PT> PBar;                    // parser group
+__device__ __forceinline__ void w32_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(W32_T) : "memory"); }
+__device__ __forceinline__ void w32_wait(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(W32_T) : "memory"); }
+constexpr int W32_BAR_FULL = 3, W32_BAR_EMPTY = 4;
+
+#ifdef CVX_PHASE_TIMING
+#define W32_PH_DECL long long ph_last = clock64(); unsigned long long ph_acc[12] = {0}
+#define W32_PH(i) do { if (ptid == 0) { long long c_ = clock64(); ph_acc[i] += (unsigned long long)(c_ - ph_last); ph_last = c_; } } while (0)
+#define W32_PH_FLUSH do { if (ptid == 0) for (int i_ = 6; i_ < 10; ++i_) atomicAdd(&g_phase[1][i_], ph_acc[i_]); } while (0)
+#else
+#define W32_PH_DECL
+#define W32_PH(i)
+#define W32_PH_FLUSH
+#endif
+
+// speculative entry state of chunk c (two chunks of look-back, exact through chunk 0)
+__device__ __forceinline__ int w32_spec_entry(const uint64_t* w64, int c, int entry)
+{
+    int d = 0, dummy = 0;
+    chunk8_walk<false>(w64[c >= 2 ? c - 2 : 0], 0ull, d, dummy);
+    d = (c == 1) ? entry : d;
+    chunk8_walk<false>(w64[c >= 1 ? c - 1 : 0], 0ull, d, dummy);
+    return (c == 0) ? entry : d;
+}
+
+// list entries (values the reference decoder stores, zeros of runs excluded) of the tokens starting in a chunk
+__device__ __forceinline__ int w32_count_entries(uint32_t mask, uint64_t A, uint64_t N)
+{
+    int n = 0;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const bool st = ((mask >> p) & 1u) != 0;
+        const int c = (int)(int8_t)((uint32_t)(A >> (8 * p)) & 0xFFu);
+        const uint32_t op = chunk8_operand(A, N, p);
+        const bool lit = (uint32_t)(c + 124) <= 248u;
+        int q = c;
+        q = (c == VLESC2) ? (int)(int16_t)(op & 0xFFFFu) : q;
+        q = (c == VLESC3) ? ((int)(op << 8) >> 8) : q;
+        int e = ((lit || c == VLESC2 || c == VLESC3) && q != 0) ? 1 : 0;
+        e = (c == VLESC4) ? 1 : e;
+        e = (c == VLESC2_8x || c == VLESC3_8x) ? 8 : e;
+        n += st ? e : 0;
+    }
+    return n;
+}
+
+// VLESC4 and the 8-value tokens, out of line: writes 1 or 8 entries at `out`
+__device__ __noinline__ void w32_rare_to_list(int c, uint32_t op, int k, int vi, float scalefac, const unsigned char* win, uint2* out)
+{
+    if (c == VLESC4) { *out = make_uint2((unsigned)vi, __float_as_uint(__fmul_rn(__uint_as_float(op), scalefac))); return; }
+    for (int j = 0; j < 8; ++j) {
+        int v;
+        if (c == VLESC2_8x) v = (int)(int16_t)((uint32_t)win[k + 2 * j] | ((uint32_t)win[k + 2 * j + 1] << 8));
+        else v = (int)((uint32_t)win[k + 3 * j] << 8 | (uint32_t)win[k + 3 * j + 1] << 16 | (uint32_t)win[k + 3 * j + 2] << 24) >> 8;
+        out[j] = make_uint2((unsigned)(vi + j), __float_as_uint(__fmul_rn(scalefac, (float)v)));
+    }
+}
+
+// expansion of one chunk into list entries (same token semantics as chunk8_expand); returns the advanced raster index
+__device__ __forceinline__ int w32_expand_list(uint32_t mask, uint64_t A, uint64_t N, int base, int vi, float scalefac,
+                                               const unsigned char* win, uint2*& out)
+{
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const bool st = ((mask >> p) & 1u) != 0;
+        const int c = (int)(int8_t)((uint32_t)(A >> (8 * p)) & 0xFFu);
+        const uint32_t op = chunk8_operand(A, N, p);
+        const bool lit = (uint32_t)(c + 124) <= 248u;
+        const bool v2 = (c == VLESC2), v3 = (c == VLESC3);
+        int q = c;
+        q = v2 ? (int)(int16_t)(op & 0xFFFFu) : q;
+        q = v3 ? ((int)(op << 8) >> 8) : q;
+        const bool single = lit || v2 || v3;
+        if (st && single && q != 0) *out++ = make_uint2((unsigned)vi, __float_as_uint(__fmul_rn((float)q, scalefac)));
+        int adv = (c == RLESC1) ? (int)(op & 0xFFu) : 1;
+        adv = (c == RLESC3) ? (int)(op & 0xFFFFFFu) : adv;
+        const bool is8 = (c == VLESC2_8x || c == VLESC3_8x);
+        if (st && (c == VLESC4 || is8)) {
+            w32_rare_to_list(c, op, base + p + 1, vi, scalefac, win, out);
+            out += is8 ? 8 : 1;
+        }
+        adv = is8 ? 8 : adv;
+        vi += st ? adv : 0;
+    }
+    return vi;
+}
+
+// The parser group's work on one block.  Returns (to every parser thread) the number of list entries, or -1 when
+// the block must be decoded in line.
+__device__ __forceinline__ int w32_parse_to_list(const D32Src& b, const unsigned char* win, unsigned char* s_mask, int* s_ext,
+                                                 unsigned long long* scratch64, uint2* list)
+{
+    const int ptid = threadIdx.x - W32_TT;
+    const uint64_t* w64 = reinterpret_cast<const uint64_t*>(win);
+    const int entry = (int)(reinterpret_cast<uintptr_t>(b.src) & 15);
+    const int nch = d32_nchunks(entry, b.hint);
+    const int K = (nch + W32_PT - 1) / W32_PT;
+    const int c0 = min(nch, ptid * K), c1 = min(nch, c0 + K);
+    const bool active = c0 < c1;
+    int ent = active ? w32_spec_entry(w64, c0, entry) : 0;
+    int ext = 0, cntv = 0;
+    auto walk_range = [&](int d) {
+        cntv = 0;
+        for (int c = c0; c < c1; ++c) {
+            int n = 0;
+            const uint32_t m = chunk8_walk<true>(w64[c], w64[c + 1], d, n);
+            s_mask[c] = (unsigned char)m;
+            cntv = min(cntv + min(n, 1 << 20), 1 << 20);
+        }
+        ext = d;
+    };
+    walk_range(ent);
+    for (;;) {                             // chain check over the ranges; inactive threads sit at the tail
+        s_ext[ptid] = ext;
+        PBar::sync();
+        const int want = (ptid > 0 && active) ? s_ext[ptid - 1] : ent;
+        const bool bad = want != ent;
+        if (!PBar::sync_or(bad ? 1 : 0)) break;
+        if (bad) { ent = want; walk_range(ent); }
+    }
+    int cnte = 0;
+    for (int c = c0; c < c1; ++c) cnte += w32_count_entries((uint32_t)s_mask[c], w64[c], w64[c + 1]);
+    unsigned long long total;
+    const unsigned long long ex = d32_excl_sum64<W32_PT, PBar>((unsigned long long)(unsigned)cntv | ((unsigned long long)(unsigned)cnte << 32), scratch64, total);
+    const long totv = (long)(total & 0xFFFFFFFFull), tote = (long)(total >> 32);
+    if (totv < F32_B || tote > W32_LCAP) return -1;          // wrong length hint (foreign block order) or a dense block
+    int vi = (int)(ex & 0xFFFFFFFFull);
+    uint2* out = list + (int)(ex >> 32);
+    for (int c = c0; c < c1; ++c) vi = w32_expand_list((uint32_t)s_mask[c], w64[c], w64[c + 1], 8 * c, vi, b.scalefac, win, out);
+    return (int)tote;
+}
+
+__global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
+{
+    constexpr bool EXACT = false;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    unsigned char* s_win = smem_raw + W32_OFF_WIN;
+    int* s_ext = reinterpret_cast<int*>(smem_raw + W32_OFF_EXT);
+    unsigned char* s_mask = smem_raw + W32_OFF_MASK;
+    uint2* s_list = reinterpret_cast<uint2*>(smem_raw + W32_OFF_LIST);
+    __shared__ unsigned long long scratch64[W32_TT / 32];
+    __shared__ unsigned long long pscratch64[W32_PT / 32];
+    __shared__ int s_ctl[2];                                       // [0] entries in the list, or -1: decode in line
+    __shared__ int p_ext[W32_PT];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint8_t* hi = p.payload + p.payload_bytes;
+    if ((long)blockIdx.x >= p.nblk) return;
+
+    if (tid >= W32_TT) {
+        // ------------------------------ parser group ------------------------------
+        const int ptid = tid - W32_TT;
+        int it = 0;
+        W32_PH_DECL;
+        for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, ++it) {
+            const D32Src b = d32_locate(p, t);
+            const int entry = (int)(reinterpret_cast<uintptr_t>(b.src) & 15);
+            const bool servable = !b.raw && b.hint > 0 && entry + b.hint <= D32_CH * 8;
+            int n = -1;
+            if (servable) {
+                const uint8_t* cbase = b.src - entry;
+                for (int g = ptid; g < D32_WIN / 16; g += W32_PT) {
+                    const uint8_t* a = cbase + 16 * g;
+                    long left = hi - a;
+                    int nb = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
+                    cp_async16_zfill(s_win + 16 * g, nb > 0 ? a : cbase, nb);
+                }
+                cp_async_commit();
+                cp_async_wait_all();
+                PBar::sync();
+            }
+            W32_PH(6);
+            if (it > 0) w32_wait(W32_BAR_EMPTY);                   // the previous list has been scattered
+            W32_PH(7);
+            if (servable) n = w32_parse_to_list(b, s_win, s_mask, p_ext, pscratch64, s_list);
+            if (ptid == 0) s_ctl[0] = n;
+            __threadfence_block();
+            w32_arrive(W32_BAR_FULL);
+            W32_PH(8);
+        }
+        W32_PH_FLUSH;
+        if (it > 0) w32_wait(W32_BAR_EMPTY);                       // match the transform group's last arrival
+        return;
+    }
+    // ------------------------------ transform group ------------------------------
+    const long plane = (long)p.g.nx * p.g.ny;
+    {
+        float4* z4 = reinterpret_cast<float4*>(sm);
+#pragma unroll
+        for (int i = 0; i < F32_B / 4 / W32_TT; ++i) z4[tid + W32_TT * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    unsigned char* win2 = s_win + D32_WIN;                          // window of the in-line path
+    CVX_PH_DECL;
+    for (long t = blockIdx.x; t < p.nblk; t += gridDim.x) {
+        CVX_PH(5);
+        w32_wait(W32_BAR_FULL);                                     // also orders every thread's zeroing before the scatter
+        CVX_PH(0);
+        const int n = s_ctl[0];
+        if (n >= 0) {
+            for (int i = tid; i < n; i += W32_TT) {
+                const uint2 e = s_list[i];
+                if (e.x < (unsigned)F32_B) sm[physr((int)e.x, 5)] = __uint_as_float(e.y);
+            }
+        } else {
+            const D32Src cur = d32_locate(p, t);
+            if (cur.raw) {                                          // CvxCompress.cpp:555: B fp32 coefficients
+                for (int i = tid; i < F32_B; i += W32_TT) {
+                    uint32_t u = 0;
+                    const uint8_t* s = cur.src + 4L * i;
+                    if ((reinterpret_cast<uintptr_t>(cur.src) & 3) == 0 && s + 4 <= hi) u = *reinterpret_cast<const uint32_t*>(s);
+                    else for (int k = 0; k < 4; ++k) if (s + k < hi) u |= (uint32_t)s[k] << (8 * k);
+                    sm[physr(i, 5)] = __uint_as_float(u);
+                }
+            } else {
+                const int entry = (int)(reinterpret_cast<uintptr_t>(cur.src) & 15);
+                for (int g = tid; g < D32_WIN / 16; g += W32_TT) {
+                    const uint8_t* a = cur.src - entry + 16 * g;
+                    long left = hi - a;
+                    int nb = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
+                    cp_async16_zfill(win2 + 16 * g, nb > 0 ? a : cur.src - entry, nb);
+                }
+                cp_async_commit();
+                cp_async_wait_all();
+                TBar::sync();
+                D32Walk wk;
+                d32_walk<W32_TT>(win2, entry, d32_nchunks(entry, cur.hint), wk);
+                d32_parse<W32_TT, TBar>(hi, cur, win2, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
+            }
+        }
+        TBar::sync();                                               // block complete, s_ctl and the list consumed
+        w32_arrive(W32_BAR_EMPTY);
+        CVX_PH(1);
+        f32_pass_xT<EXACT, false, W32_TT>(sm);
+        __syncwarp();
+        f32_pass_yT<EXACT, false, W32_TT>(sm);
+        TBar::sync();
+        CVX_PH(2);
+        typename LineOf<EXACT, W32_TT>::type v[32];
+        {
+            float* zl = f32_zline(sm, tid);
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                float* e = zl + reg_to_sub<32, EXACT>(r) * 1024;
+                p_set(v[r], e[0], e[512]);
+            }
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
+        }
+        const int iix = (int)(t % p.nbx);
+        const long q = t / p.nbx;
+        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        const int gx = iix * 32 + lane, gz0 = iiz * 32;
+        const int nzl = min(32, p.g.nz - gz0);
+        inv_line<32, EXACT>(v);
+        CVX_PH(3);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int gy = iiy * 32 + warp + 16 * k;
+            if (gx < p.g.nx && gy < p.g.ny) {
+                float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
+                if (nzl == 32) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { if (j < nzl) *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
+                }
+            }
+        }
+    }
+    CVX_PH(5);
+    CVX_PH_FLUSH(1);
+}

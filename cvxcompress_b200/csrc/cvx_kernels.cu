@@ -16,6 +16,7 @@
 #include <stdint.h>
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include "cvx_wavelet.cuh"
 #include "cvx_rle.cuh"
 #include "cvx_device.cuh"
@@ -524,6 +525,7 @@ __global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams p)
 }
 
 #include "cvx_decode32.inl"
+#include "cvx_decode32ws.inl"
 
 // forward / inverse transform of dense blocks: block k is the z-range [k*bz, (k+1)*bz) of a
 // bx * by * (bz*nblocks) volume
@@ -903,11 +905,19 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
         // the headline shape: prefetched payload windows, z lines in registers, direct row stores (cvx_decode32.inl)
         // 512 threads, two lines per thread.  (A 1024-thread / 64-register / one-line-per-thread instantiation of the same
         // template was measured 12 % slower -- 3.47 vs 3.10 ms: the phases are pipe-throughput bound, not latency bound.)
+        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
+        static const bool no_ws = getenv("CVX_GPU_NO_WS") != nullptr;       // developer switch: the fused (non-specialised) kernel
+        if (!exact && !no_ws) {
+            // LIFTING: warp-specialised kernel, the parse of block t+1 overlaps the transform of block t (cvx_decode32ws.inl)
+            e = cudaFuncSetAttribute(k_decode32ws, cudaFuncAttributeMaxDynamicSharedMemorySize, W32_SMEM);
+            if (e != cudaSuccess) return e;
+            k_decode32ws<<<(unsigned)grid, W32_T, W32_SMEM, st>>>(p);
+            return cudaGetLastError();
+        }
         auto kern = exact ? k_decode32<true, 512> : k_decode32<false, 512>;
         const int threads = 512;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, D32_SMEM);
         if (e != cudaSuccess) return e;
-        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
         kern<<<(unsigned)grid, threads, D32_SMEM, st>>>(p);
         return cudaGetLastError();
     }

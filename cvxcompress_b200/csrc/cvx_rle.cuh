@@ -380,7 +380,7 @@ CVX_HD_NOINLINE int chunk8_rare(int c, uint32_t op, int k, int vi, int num, floa
 // of the first value; zeros are not written (pre-zeroed destination).  getb(k) = byte k of the staged window,
 // base = window index of this chunk's first byte.  getb / put must be cheap to copy (they are passed by value).
 template <class GetB, class PutV>
-CVX_HD void chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int vi, int num, float scalefac, GetB getb, PutV put)
+CVX_HD int chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int vi, int num, float scalefac, GetB getb, PutV put)
 {
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
@@ -400,6 +400,7 @@ CVX_HD void chunk8_expand(uint32_t mask, uint64_t A, uint64_t N, int base, int v
         if (st && !single && c != RLESC1) adv = chunk8_rare(c, op, base + p + 1, vi, num, scalefac, getb, put);
         vi += st ? adv : 0;
     }
+    return vi;                            // raster index after the chunk's last token
 }
 
 }  // namespace cvx
