@@ -58,7 +58,8 @@ def lib():
         import torch  # noqa: F401  (loads the CUDA runtime the library links against)
     except Exception:
         pass
-    L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    # RTLD_LOCAL: the reference build under oracle/_ref defines the same CvxCompress:: symbols; neither may interpose the other
+    L = C.CDLL(LIB_PATH, mode=C.RTLD_LOCAL)
     i, l, f, p = C.c_int, C.c_long, C.c_float, C.c_void_p
     L.cvxgpu_last_error.restype = C.c_char_p
     L.cvxgpu_last_error.argtypes = []

@@ -70,3 +70,21 @@ def test_no_cpu_fallback_without_a_device():
     rc = L.cvxgpu_compress(vol.ctypes.data, 8, 8, 8, 8, 8, 8, 1e-2, 0, out.ctypes.data, C.byref(ln), C.byref(ratio))
     assert rc == _lib.ERR_CUDA
     assert L.cvxgpu_last_error()
+
+
+def test_product_and_reference_libraries_do_not_interpose():
+    """both libraries define CvxCompress::*; each is linked -Bsymbolic and loaded RTLD_LOCAL so that the reference
+    build (the checker) never runs product code and vice versa, whatever the load order"""
+    import oracle_libs as ol
+    for path in (_lib.LIB_PATH,) + ((ol.REF_SO,) if ol.have_ref() else ()):
+        dyn = subprocess.run(["readelf", "-d", path], stdout=subprocess.PIPE, text=True, check=True).stdout
+        assert "SYMBOLIC" in dyn, path
+    if not ol.have_ref():
+        pytest.skip("oracle/_ref not built")
+    _lib.lib()                                     # product library first: the order bench.py uses
+    import numpy as np
+    from cvxcompress_b200 import synth
+    vol = synth.g2(24, 16, 16)
+    s, _ = ol.ref_compress(vol, 8, 8, 8, 1e-2)     # would abort (no GPU) or run GPU code if interposed
+    want, _ = ol.oracle_compress(vol, 8, 8, 8, 1e-2, False)
+    assert bytes(s[:len(s) - 7]) == bytes(want[:len(want) - 7])
