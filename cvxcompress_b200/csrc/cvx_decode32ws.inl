@@ -13,7 +13,7 @@
 // in line by the transform group with the k_decode32 routines on a named barrier.
 
 constexpr int W32_TT = 512;                          // transform threads (warps 0..15)
-constexpr int W32_PT = 128;                          // parser threads (warps 16..19)
+constexpr int W32_PT = 256;                          // parser threads (warps 16..19)
 constexpr int W32_T = W32_TT + W32_PT;
 constexpr int W32_LCAP = 6144;                       // list entries (8 bytes each)
 constexpr int W32_OFF_WIN = F32_B * 4;               // parser window, then the in-line window
@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
 
     if (tid >= W32_TT) {
         // ------------------------------ parser group ------------------------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
         const int ptid = tid - W32_TT;
         int it = 0;
         W32_PH_DECL;
@@ -209,6 +210,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         return;
     }
     // ------------------------------ transform group ------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
     const long plane = (long)p.g.nx * p.g.ny;
     {
         float4* z4 = reinterpret_cast<float4*>(sm);

@@ -88,6 +88,7 @@ def main():
     ap.add_argument("--lib", default=os.path.join(ROOT, "cvxcompress_b200", "lib", "libcvxcompress.so"))
     ap.add_argument("--kernel", default=".*")
     ap.add_argument("--top", type=int, default=25)
+    ap.add_argument("--focus", default=None, help="file:line of the kernel body: stall reasons and opcode mix of that call site only")
     args = ap.parse_args()
     sass = sass_lines(args.lib)
     dm = demangle(list(sass.keys()))
@@ -112,6 +113,25 @@ def main():
         outer = collections.defaultdict(lambda: [0.0, 0.0, 0.0])
         stalls = collections.Counter()
         opc = collections.Counter()
+        if args.focus:
+            ff, fl = args.focus.rsplit(":", 1)
+            pairs = [(r, s) for r, s in zip(rows, sass[key]) if s[4].endswith(ff) and s[5] == int(fl)]
+            fi = sum(float(r["Instructions Executed"] or 0) for r, _ in pairs)
+            fs = sum(float(r["# Samples"] or 0) for r, _ in pairs) or 1.0
+            st, oc, sub = collections.Counter(), collections.Counter(), collections.defaultdict(lambda: [0.0, 0.0])
+            for r, s in pairs:
+                ie = float(r["Instructions Executed"] or 0)
+                oc[s[6].split()[0] if not s[6].startswith("@") else s[6].split()[1]] += ie
+                sub[(s[2], s[3])][0] += ie; sub[(s[2], s[3])][1] += float(r["# Samples"] or 0)
+                for c, v in r.items():
+                    if c.startswith("stall_") and "Not Issued" not in c and v:
+                        st[c] += float(v)
+            print("  focus %s: %d SASS, inst %.2f%% of kernel, samples %.2f%%" % (args.focus, len(pairs), 100 * fi / tot_i, 100 * fs / tot_s))
+            print("    stalls: " + ", ".join("%s %.1f%%" % (k[6:], 100 * v / fs) for k, v in st.most_common(10)))
+            print("    opcodes: " + ", ".join("%s %.1f%%" % (k, 100 * v / (fi or 1)) for k, v in oc.most_common(16)))
+            for k, v in sorted(sub.items(), key=lambda kv: -kv[1][1])[:args.top]:
+                print("     %6.2f  %6.2f   %s:%d" % (100 * v[0] / (fi or 1), 100 * v[1] / fs, k[0], k[1]))
+            continue
         for r, s in zip(rows, sass[key]):
             ie, ns, te = float(r["Instructions Executed"] or 0), float(r["# Samples"] or 0), float(r["Thread Instructions Executed"] or 0)
             for d, k in ((inner, (s[0], s[1])), (mid, (s[2], s[3])), (outer, (s[4], s[5]))):
