@@ -39,23 +39,6 @@ __device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8
     cp_async_commit();
 }
 
-// barrier policies: the whole CTA, or a named barrier over a subset of its warps (warp-specialised kernel)
-struct CtaBar {
-    __device__ __forceinline__ static void sync() { __syncthreads(); }
-    __device__ __forceinline__ static int sync_or(int pred) { return __syncthreads_or(pred); }
-};
-template <int ID, int N>
-struct NamedBar {
-    __device__ __forceinline__ static void sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
-    __device__ __forceinline__ static int sync_or(int pred)
-    {
-        int r;
-        asm volatile("{\n.reg .pred p, q;\nsetp.ne.s32 q, %1, 0;\nbar.red.or.pred p, %2, %3, q;\nselp.s32 %0, 1, 0, p;\n}"
-                     : "=r"(r) : "r"(pred), "n"(ID), "n"(N) : "memory");
-        return r;
-    }
-};
-
 // exclusive sum of a pair of 32-bit counts packed in 64 bits (each count <= 2^20, 512 threads: no carry between halves)
 template <int T, class Bar>
 __device__ __forceinline__ unsigned long long d32_excl_sum64(unsigned long long v, unsigned long long* scratch64, unsigned long long& total)

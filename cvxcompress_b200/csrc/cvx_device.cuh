@@ -31,21 +31,41 @@ struct NoSwz {
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 __device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
 
+// barrier policies: the whole CTA, or a named barrier over a subset of its warps (warp-specialised kernel)
+struct CtaBar {
+    __device__ __forceinline__ static void sync() { __syncthreads(); }
+    __device__ __forceinline__ static int sync_or(int pred) { return __syncthreads_or(pred); }
+};
+template <int ID, int N>
+struct NamedBar {
+    __device__ __forceinline__ static void sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
+    __device__ __forceinline__ static int sync_or(int pred)
+    {
+        int r;
+        asm volatile("{\n.reg .pred p, q;\nsetp.ne.s32 q, %1, 0;\nbar.red.or.pred p, %2, %3, q;\nselp.s32 %0, 1, 0, p;\n}"
+                     : "=r"(r) : "r"(pred), "n"(ID), "n"(N) : "memory");
+        return r;
+    }
+};
+
 // ---- CTA scans ---------------------------------------------------------------------------
+// T threads of a thread group that starts at a multiple of T (the whole CTA, or one side of a warp-specialised
+// kernel); Bar is the group's barrier.
 // exclusive sum over the CTA; `total` receives the CTA-wide sum.  scratch: >= 33 ints.
-template <int T>
+template <int T, class Bar = CtaBar>
 __device__ __forceinline__ int cta_excl_sum(int v, int* scratch, int& total)
 {
     constexpr int NW = (T + 31) / 32;
+    const int gw = warp_id() % NW;
     int x = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         int y = __shfl_up_sync(0xffffffffu, x, d);
         if (lane_id() >= d) x += y;
     }
-    if (lane_id() == 31) scratch[warp_id()] = x;
-    __syncthreads();
-    if (warp_id() == 0) {
+    if (lane_id() == 31) scratch[gw] = x;
+    Bar::sync();
+    if (gw == 0) {
         int w = lane_id() < NW ? scratch[lane_id()] : 0;
         int s = w;
 #pragma unroll
@@ -56,10 +76,10 @@ __device__ __forceinline__ int cta_excl_sum(int v, int* scratch, int& total)
         if (lane_id() < NW) scratch[lane_id()] = s - w;
         if (lane_id() == 31) scratch[32] = s;
     }
-    __syncthreads();
-    int r = scratch[warp_id()] + x - v;
+    Bar::sync();
+    int r = scratch[gw] + x - v;
     total = scratch[32];
-    __syncthreads();
+    Bar::sync();
     return r;
 }
 

@@ -12,15 +12,18 @@ __device__ __forceinline__ void publish_aggregate(const EncParams& p, long t, un
     st_release_u64(&p.status[t], (t == 0 ? CVX_ST_PFX : CVX_ST_AGG) | len);
 }
 
-// all F32_T threads; returns the exclusive prefix of ticket t to every thread.  scratch64: >= 18 words.
+// all GT threads of the group; returns the exclusive prefix of ticket t to every thread.  scratch64: >= GT/32 words.
+template <int GT = F32_T, class Bar = CtaBar>
 __device__ __forceinline__ unsigned long long wide_lookback(const EncParams& p, long t, unsigned long long len, bool raw,
                                                             unsigned long long* scratch64)
 {
+    static_assert((GT & (GT - 1)) == 0, "group size is a power of two");
+    const int gtid = threadIdx.x & (GT - 1), gwarp = gtid >> 5;
     unsigned long long excl = 0;
     if (t > 0) {
         long j = t - 1;
         for (;;) {
-            const long idx = j - threadIdx.x;
+            const long idx = j - gtid;
             unsigned long long s = CVX_ST_PFX;                      // before ticket 0: prefix 0
             if (idx >= 0) {
                 do { s = ld_acquire_u64(&p.status[idx]); } while ((s >> 62) == 0);
@@ -30,21 +33,21 @@ __device__ __forceinline__ unsigned long long wide_lookback(const EncParams& p, 
             unsigned long long v = (lane_id() <= first) ? (s & CVX_ST_MASK) : 0ull;
 #pragma unroll
             for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-            if (lane_id() == 0) scratch64[warp_id()] = v | (pfx ? (1ull << 63) : 0ull);
-            __syncthreads();
+            if (lane_id() == 0) scratch64[gwarp] = v | (pfx ? (1ull << 63) : 0ull);
+            Bar::sync();
             bool done = false;
-            for (int w = 0; w < F32_T / 32; ++w) {                  // warps in look-back order; stop at the first prefix
+            for (int w = 0; w < GT / 32; ++w) {                  // warps in look-back order; stop at the first prefix
                 const unsigned long long x = scratch64[w];
                 excl += x & ~(1ull << 63);
                 if (x >> 63) { done = true; break; }
             }
-            __syncthreads();
+            Bar::sync();
             if (done) break;
-            j -= F32_T;
+            j -= GT;
         }
-        if (threadIdx.x == 0) st_release_u64(&p.status[t], CVX_ST_PFX | (excl + len));
+        if (gtid == 0) st_release_u64(&p.status[t], CVX_ST_PFX | (excl + len));
     }
-    if (threadIdx.x == 0) {
+    if (gtid == 0) {
         p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);      // CvxCompress.cpp:382-384
         if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + len);
     }

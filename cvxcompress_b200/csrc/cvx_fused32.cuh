@@ -308,7 +308,7 @@ __device__ __forceinline__ EntryTok entry_token(uint2 ent, int prev_idx, float m
 template <int T>
 __device__ __forceinline__ void f32_mark_groups(uint2* list, int n, float mulfac)
 {
-    for (int e = threadIdx.x; e + 7 < n; e += T) {
+    for (int e = threadIdx.x & (T - 1); e + 7 < n; e += T) {
         const int idx = (int)(list[e].x & F32_IDX_MASK);
         if ((idx & 7) != 0 || (int)(list[e + 7].x & F32_IDX_MASK) != idx + 7) continue;
         int q8[8];
@@ -363,16 +363,17 @@ __device__ __forceinline__ void put_entry_branchfree(unsigned char* out, int pos
 }
 
 // staged payload (shared memory, 16-byte aligned) -> global, any destination alignment: 32-bit coalesced stores
+template <int GT = F32_T>
 __device__ __forceinline__ void copy_out(unsigned char* dst, const unsigned char* stage, int len)
 {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x & (GT - 1);
     int head = (int)((4u - (unsigned)(reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u);
     if (head > len) head = len;
     if (tid < head) dst[tid] = stage[tid];
     const int nw = (len - head) >> 2;
     uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
     const uint32_t* s32 = reinterpret_cast<const uint32_t*>(stage);
-    for (int k = tid; k < nw; k += F32_T) {
+    for (int k = tid; k < nw; k += GT) {
         const uint32_t lo = s32[k];
         d32[k] = head ? __funnelshift_r(lo, s32[k + 1], 8 * head) : lo;
     }

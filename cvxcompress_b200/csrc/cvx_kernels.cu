@@ -449,6 +449,7 @@ __global__ void __launch_bounds__(T, MINB) k_encode_fused(const EncParams p)
 }
 
 #include "cvx_encode32.inl"
+#include "cvx_encode32ws.inl"
 
 // ------------------------------------------------------------------------------------------
 // Fused decode
@@ -848,10 +849,18 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
         // the headline shape: TMA-fed persistent kernel with the sparse coder (cvx_fused32.cuh)
         CUtensorMap tmap;
         const int use_tma = make_volume_tmap(&tmap, d_vol, s.nx, s.ny, s.nz, 32, 32, 8) ? 1 : 0;
+        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
+        static const bool no_ws = getenv("CVX_GPU_NO_WS") != nullptr;       // developer switch: the fused (non-specialised) kernel
+        if (!exact && !use_local && use_tma && !no_ws) {
+            // LIFTING, global RMS: warp-specialised kernel, the coder of block t overlaps the transform of block t+1
+            e = cudaFuncSetAttribute(k_encode32ws, cudaFuncAttributeMaxDynamicSharedMemorySize, E32_SMEM);
+            if (e != cudaSuccess) return e;
+            k_encode32ws<<<(unsigned)grid, E32_T, E32_SMEM, st>>>(tmap, p);
+            return cudaGetLastError();
+        }
         auto kern = exact ? k_encode32<true> : k_encode32<false>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F32_SMEM);
         if (e != cudaSuccess) return e;
-        long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
         kern<<<(unsigned)grid, F32_T, F32_SMEM, st>>>(tmap, p, use_tma);
         return cudaGetLastError();
     }
