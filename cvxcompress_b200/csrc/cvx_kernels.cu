@@ -821,6 +821,16 @@ static cudaError_t launch_persistent(K kernel, int T, size_t smem, long nwork, i
         else { if (exact) CALL(32, true, 128, 4); else CALL(32, false, 128, 4); }                        \
     } while (0)
 
+// developer switch between the warp-specialised 32^3 kernels (default) and the fused ones they were derived from:
+// environment CVX_GPU_NO_WS at load, or cvx_debug_set_ws() (tests compare the two bit for bit)
+static int g_ws = -1;
+static bool ws_enabled()
+{
+    if (g_ws < 0) g_ws = getenv("CVX_GPU_NO_WS") ? 0 : 1;
+    return g_ws != 0;
+}
+extern "C" void cvx_debug_set_ws(int on) { g_ws = on ? 1 : 0; }
+
 static void rle_segments(const BlkShape& b, int& nseg, int& gps)
 {
     int V = b.B / SEG_CAP;
@@ -850,8 +860,7 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
         CUtensorMap tmap;
         const int use_tma = make_volume_tmap(&tmap, d_vol, s.nx, s.ny, s.nz, 32, 32, 8) ? 1 : 0;
         long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
-        static const bool no_ws = getenv("CVX_GPU_NO_WS") != nullptr;       // developer switch: the fused (non-specialised) kernel
-        if (!exact && !use_local && use_tma && !no_ws) {
+        if (!exact && !use_local && use_tma && ws_enabled()) {
             // LIFTING, global RMS: warp-specialised kernel, the coder of block t overlaps the transform of block t+1
             e = cudaFuncSetAttribute(k_encode32ws, cudaFuncAttributeMaxDynamicSharedMemorySize, E32_SMEM);
             if (e != cudaSuccess) return e;
@@ -915,8 +924,7 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
         // 512 threads, two lines per thread.  (A 1024-thread / 64-register / one-line-per-thread instantiation of the same
         // template was measured 12 % slower -- 3.47 vs 3.10 ms: the phases are pipe-throughput bound, not latency bound.)
         long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
-        static const bool no_ws = getenv("CVX_GPU_NO_WS") != nullptr;       // developer switch: the fused (non-specialised) kernel
-        if (!exact && !no_ws) {
+        if (!exact && ws_enabled()) {
             // LIFTING: warp-specialised kernel, the parse of block t+1 overlaps the transform of block t (cvx_decode32ws.inl)
             e = cudaFuncSetAttribute(k_decode32ws, cudaFuncAttributeMaxDynamicSharedMemorySize, W32_SMEM);
             if (e != cudaSuccess) return e;

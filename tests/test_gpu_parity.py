@@ -385,3 +385,41 @@ def test_run_module_tests(gpu):
     fn.argtypes = [C.c_void_p, C.c_bool, C.c_bool]
     this = (C.c_char * 64)()                 # the class has no data members beyond its vptr, which the method does not use
     assert fn(C.addressof(this), False, False)
+
+
+WS_CASES = [c for c in CASES if c[4:7] == (32, 32, 32)] + [
+    ("noise", 96, 64, 64, 32, 32, 32, 3e-4),         # payloads above the parser's 8 KiB window: in-line decode
+    ("noise", 96, 64, 64, 32, 32, 32, 3e-7),         # mix of raw and dense blocks next to sparse ones
+    ("g2", 1056, 96, 64, 32, 32, 32, 1e-2),          # more blocks than CTAs: long hand-over chains
+    ("g2", 33, 31, 95, 32, 32, 32, 1e-3),            # fewer blocks than list buffers per CTA
+]
+
+
+@pytest.mark.parametrize("case", WS_CASES, ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_warp_specialised_kernels_equal_fused_kernels(gpu, case):
+    """LIFTING mode: k_encode32ws / k_decode32ws (coder and parser on their own warps) against k_encode32 / k_decode32,
+    which run the same arithmetic in the same order: streams and reconstructions must agree bit for bit.  The fused
+    kernels' integer paths are pinned to the oracle by the EXACT-mode tests above."""
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    from cvxcompress_b200 import _lib
+    vol = _vol(kind, nx, ny, nz)
+    L = _lib.lib()
+    gpu.set_transform("lifting")
+    try:
+        out = {}
+        for ws in (1, 0):
+            L.cvx_debug_set_ws(ws)
+            got, ratio = _gpu_compress(gpu, vol, bx, by, bz, scale, False)
+            out[ws] = (got, _gpu_decompress(gpu, got, nx, ny, nz))
+        L.cvx_debug_set_ws(1)
+        cross = _gpu_decompress(gpu, out[0][0], nx, ny, nz)          # fused encoder's stream through the WS decoder
+    finally:
+        L.cvx_debug_set_ws(1)
+        gpu.set_transform("exact")
+    assert _streams_equal(out[1][0], out[0][0])
+    assert np.array_equal(out[1][1].view(np.uint32), out[0][1].view(np.uint32))
+    assert np.array_equal(cross.view(np.uint32), out[0][1].view(np.uint32))
+    # and the stream is a valid CvxCompress stream: the oracle's decoder reproduces it within the LIFTING tolerance
+    ref = ol.oracle_decompress(out[1][0], nx, ny, nz)
+    scale_abs = float(np.max(np.abs(vol))) or 1.0
+    assert float(np.max(np.abs(ref - out[1][1]))) <= 2e-5 * scale_abs
