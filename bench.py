@@ -301,13 +301,24 @@ def run_ours(args):
 
     do_decompress()
     torch.cuda.synchronize()
-    # quality of the round trip (also proves the timed work is the real work)
-    num = torch.sum((slab.double() - out_slab.double()) ** 2)
-    den = torch.sum(slab.double() ** 2)
-    if world > 1:
-        nd = torch.stack([num, den]); dist.all_reduce(nd); num, den = nd[0], nd[1]
-    err = float(torch.sqrt(num / den).item())
+    # quality of the round trip (also proves the timed work is the real work): checked here and again after the last
+    # timed decode; a result outside the quantiser's error bound voids the run (exit code 3, no JSON line)
     import math
+
+    def roundtrip_error():
+        num = torch.sum((slab.double() - out_slab.double()) ** 2)
+        den = torch.sum(slab.double() ** 2)
+        if world > 1:
+            nd = torch.stack([num, den]); dist.all_reduce(nd); num, den = nd[0], nd[1]
+        return float(torch.sqrt(num / den).item())
+
+    def check_quality(e, where):
+        if not (math.isfinite(e) and e < SCALE):
+            sys.stderr.write("bench.py: INVALID RUN: round-trip error %r %s (bound %g)\n" % (e, where, SCALE))
+            sys.exit(3)
+
+    err = roundtrip_error()
+    check_quality(err, "after the first Decompress")
     snr = -20.0 * math.log10(err) if err > 0 else float("inf")
 
     for _ in range(W):
@@ -407,6 +418,9 @@ def run_ours(args):
                                "compress_frac": (8 * cells_rank + stream_slab_bytes) / (tc_ms * 1e-3) / 1e9 / peak,
                                "decompress_frac": (4 * cells_rank + stream_slab_bytes) / (td_ms * 1e-3) / 1e9 / peak}}
     del pay_t, offs_t
+    err_end = roundtrip_error()                     # out_slab now holds the last timed k_decode launch's output
+    check_quality(err_end, "after the timed region")
+    err = max(err, err_end)
 
     # -- end to end through the reference-facing call with HOST buffers (pinned), copies inside the timed region --
     e2e = None
