@@ -38,47 +38,6 @@ constexpr int W32_BAR_FULL = 3, W32_BAR_EMPTY = 4;
 #define W32_PH_FLUSH
 #endif
 
-// ---- z-interleaved block layout of this kernel ----------------------------------------------------------------
-// Cells (x, y, z) and (x, y, z + 16) are neighbours in shared memory: row pair rp = (z & 15)*32 + y holds 64 floats,
-// logical position 2x + (z >> 4); its sixteen 16-byte chunks are XOR-swizzled by y & 7.  The x pass then loads a row
-// PAIR as sixteen 128-bit words whose 64-bit halves are ready-made packed operands (FFMA2/FADD2 -- half the FP32
-// instructions of two scalar rows), the y pass and the z loads move one 64-bit pair per access, all conflict-free.
-__device__ __forceinline__ int z2_phys(int idx)
-{
-    const int x = idx & 31, y = (idx >> 5) & 31, z = idx >> 10;
-    return ((z & 15) * 32 + y) * 64 + ((((x >> 1) ^ (y & 7)) << 2) | ((x & 1) << 1) | (z >> 4));
-}
-// x pass (inverse): thread tid owns row pair tid = (zz = warp, y = lane)
-__device__ __forceinline__ void z2_pass_x_inv(float* sm)
-{
-    ulonglong2* row = reinterpret_cast<ulonglong2*>(sm + threadIdx.x * 64);
-    const int k = threadIdx.x & 7;
-    F2 v[32];
-#pragma unroll
-    for (int c = 0; c < 16; ++c) {
-        const ulonglong2 q = row[c ^ k];
-        v[sub_to_reg<32, false>(2 * c)].u = q.x;
-        v[sub_to_reg<32, false>(2 * c + 1)].u = q.y;
-    }
-    inv_line<32, false>(v);
-#pragma unroll
-    for (int c = 0; c < 16; ++c) row[c ^ k] = make_ulonglong2(v[2 * c].u, v[2 * c + 1].u);
-}
-// y pass (inverse): thread (x = lane, zz = warp) owns the y lines of z = zz and zz + 16, one 64-bit pair per cell
-__device__ __forceinline__ void z2_pass_y_inv(float* sm)
-{
-    const int x = threadIdx.x & 31, zz = threadIdx.x >> 5;
-    unsigned long long* a[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = reinterpret_cast<unsigned long long*>(sm + zz * 2048 + ((((x >> 1) ^ k) << 2) | ((x & 1) << 1)));
-    F2 v[32];
-#pragma unroll
-    for (int r = 0; r < 32; ++r) { const int s = reg_to_sub<32, false>(r); v[r].u = a[s & 7][s * 32]; }
-    inv_line<32, false>(v);
-#pragma unroll
-    for (int j = 0; j < 32; ++j) a[j & 7][j * 32] = v[j].u;
-}
-
 // speculative entry state of chunk c (two chunks of look-back, exact through chunk 0)
 __device__ __forceinline__ int w32_spec_entry(const uint64_t* w64, int c, int entry)
 {
@@ -269,7 +228,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         if (n >= 0) {
             for (int i = tid; i < n; i += W32_TT) {
                 const uint2 e = s_list[i];
-                if (e.x < (unsigned)F32_B) sm[z2_phys((int)e.x)] = __uint_as_float(e.y);
+                if (e.x < (unsigned)F32_B) sm[physr((int)e.x, 5)] = __uint_as_float(e.y);
             }
         } else {
             const D32Src cur = d32_locate(p, t);
@@ -279,7 +238,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
                     const uint8_t* s = cur.src + 4L * i;
                     if ((reinterpret_cast<uintptr_t>(cur.src) & 3) == 0 && s + 4 <= hi) u = *reinterpret_cast<const uint32_t*>(s);
                     else for (int k = 0; k < 4; ++k) if (s + k < hi) u |= (uint32_t)s[k] << (8 * k);
-                    sm[z2_phys(i)] = __uint_as_float(u);
+                    sm[physr(i, 5)] = __uint_as_float(u);
                 }
             } else {
                 const int entry = (int)(reinterpret_cast<uintptr_t>(cur.src) & 15);
@@ -294,29 +253,27 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
                 TBar::sync();
                 D32Walk wk;
                 d32_walk<W32_TT>(win2, entry, d32_nchunks(entry, cur.hint), wk);
-                d32_parse<W32_TT, TBar>(hi, cur, win2, s_ext, scratch64, wk, [sm](int i, float v) { sm[z2_phys(i)] = v; });
+                d32_parse<W32_TT, TBar>(hi, cur, win2, s_ext, scratch64, wk, [sm](int i, float v) { sm[physr(i, 5)] = v; });
             }
         }
         TBar::sync();                                               // block complete, s_ctl and the list consumed
         w32_arrive(W32_BAR_EMPTY);
         CVX_PH(1);
-        z2_pass_x_inv(sm);
-        __syncwarp();                                               // warp zz owns the rows and the y lines of z = zz, zz + 16
-        z2_pass_y_inv(sm);
+        f32_pass_xT<EXACT, false, W32_TT>(sm);
+        __syncwarp();
+        f32_pass_yT<EXACT, false, W32_TT>(sm);
         TBar::sync();
         CVX_PH(2);
         typename LineOf<EXACT, W32_TT>::type v[32];
         {
-            // thread (x = lane, y = warp + 16 k): the 64-bit word at zz*1024 (+ 512 for k = 1) holds z = zz and zz + 16
-            unsigned long long* zl = reinterpret_cast<unsigned long long*>(sm + warp * 64 + ((((lane >> 1) ^ (warp & 7)) << 2) | ((lane & 1) << 1)));
+            float* zl = f32_zline(sm, tid);
 #pragma unroll
-            for (int zz = 0; zz < 16; ++zz) {
-                const F2 a = F2{zl[zz * 1024]}, b = F2{zl[zz * 1024 + 512]};
-                p_set(v[sub_to_reg<32, EXACT>(zz)], f2_lo(a), f2_lo(b));
-                p_set(v[sub_to_reg<32, EXACT>(zz + 16)], f2_hi(a), f2_hi(b));
+            for (int r = 0; r < 32; ++r) {
+                float* e = zl + reg_to_sub<32, EXACT>(r) * 1024;
+                p_set(v[r], e[0], e[512]);
             }
 #pragma unroll
-            for (int zz = 0; zz < 16; ++zz) { zl[zz * 1024] = 0ull; zl[zz * 1024 + 512] = 0ull; }
+            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
         }
         const int iix = (int)(t % p.nbx);
         const long q = t / p.nbx;
