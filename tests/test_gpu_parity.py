@@ -451,3 +451,58 @@ def test_warp_specialised_kernels_many_blocks_per_cta(gpu):
         gpu.set_transform("exact")
     err = float(((rec0 - vol).double().pow(2).mean().sqrt() / vol.double().pow(2).mean().sqrt()))
     assert err < 6e-3
+
+
+@pytest.mark.skipif(not ol.have_ref(), reason="oracle/_ref (reference build) did not travel")
+def test_warp_specialised_decoder_foreign_block_order(gpu):
+    """A reference stream written by 8 threads has its blocks in completion order (CvxCompress.cpp:365-390): the offset
+    table no longer gives payload lengths, so the parser group declines and the transform group decodes in line.
+    LIFTING: k_decode32ws must equal k_decode32 bit for bit."""
+    from cvxcompress_b200 import _lib
+    L = _lib.lib()
+    nx, ny, nz = 151, 101, 70
+    vol = _vol("g2", nx, ny, nz)
+    ref8, _ = ol.ref_compress(vol, 32, 32, 32, 1e-2, False, threads=8)
+    gpu.set_transform("lifting")
+    try:
+        L.cvx_debug_set_ws(0)
+        want = _gpu_decompress(gpu, ref8, nx, ny, nz)
+        L.cvx_debug_set_ws(1)
+        got = _gpu_decompress(gpu, ref8, nx, ny, nz)
+    finally:
+        L.cvx_debug_set_ws(1)
+        gpu.set_transform("exact")
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    exact = ol.ref_decompress(ref8, nx, ny, nz, threads=2)
+    assert float(np.max(np.abs(exact - got))) <= 2e-5 * float(np.max(np.abs(vol)))
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("ws", [1, 0])
+def test_corrupted_payload_terminates(gpu, ws):
+    """Garbage payload bytes (valid header and offset table): the decoders must come back -- every read is clamped to the
+    stream end and every parse loop is bounded -- whatever they reconstruct."""
+    import torch
+    from cvxcompress_b200 import _lib
+    L = _lib.lib()
+    nx, ny, nz = 160, 96, 64
+    vol = torch.from_numpy(_vol("g2", nx, ny, nz)).cuda()
+    gpu.set_transform("lifting")
+    try:
+        L.cvx_debug_set_ws(ws)
+        s, ln, _ = gpu.compress_device(vol, 32, 32, 32, 1e-3)
+        nblk = 5 * 3 * 2
+        g = torch.Generator(device="cuda").manual_seed(7)
+        bad = s.clone()
+        lo = 32 + 8 * nblk
+        bad[lo:ln] = torch.randint(0, 256, (ln - lo,), dtype=torch.uint8, device="cuda", generator=g)
+        out = gpu.decompress_device(bad, ln, nx, ny, nz)
+        torch.cuda.synchronize()
+        assert out.shape == (nz, ny, nx)
+        cut = s.clone()
+        cut[ln // 2:] = 0x7D                                      # a truncated stream padded with RLESC3 bytes
+        out = gpu.decompress_device(cut, ln, nx, ny, nz)
+        torch.cuda.synchronize()
+    finally:
+        L.cvx_debug_set_ws(1)
+        gpu.set_transform("exact")
