@@ -1,4 +1,4 @@
-// cvx_encode32ws.inl -- k_encode32ws: warp-specialised 32^3 encoder (LIFTING arithmetic, global RMS), included after
+// cvx_encode32ws.inl -- k_encode32ws: warp-specialised 32^3 encoder (LIFTING arithmetic), included after
 // cvx_encode32.inl.
 //
 // k_encode32 runs transform (FMA pipe) and coder (integer pipe, half rate on this part) one after the other.  Here a
@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
     unsigned char* s_stage = smem_raw + E32_OFF_STAGE;
     __shared__ uint64_t s_bar;
     __shared__ int scratch[72];
+    __shared__ float s_red[32];
     __shared__ unsigned int s_ticket[2];
     __shared__ unsigned long long s_off;
     __shared__ unsigned long long s_lb[E32_CT / 32 + 2];
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
 
     const int tid = threadIdx.x, lane = tid & 31;
     const unsigned lt = (1u << lane) - 1u;
-    const float gmul = *p.glob_mulfac;
+    const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
 
     auto issue_load = [&](unsigned int t) {      // one thread: TMA of block t into the block buffer, 4 boxes of 32x32x8
         const int iix = (int)(t % p.nbx);

@@ -27,7 +27,20 @@
             for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
             fwd_line<32, EXACT>(vz);
         }
-        const float mulfac = gmul;
+        float mulfac = gmul;
+        if (p.use_local) {               // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348 (LIFTING: parallel fp32 reduction)
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                float* zl = f32_zline(sm, tid + E32_TT * k);
+#pragma unroll
+                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = k ? p_hi(vz[r]) : p_lo(vz[r]);
+            }
+            ETBar::sync();
+            const float ss = cta_sumsq<E32_TT, ETBar>(sm, F32_B, s_red);
+            const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
+            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+            if (tid == 0) p.blkmulfac[t] = mulfac;
+        }
         const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
         const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
 #pragma unroll
@@ -36,7 +49,7 @@
 #pragma unroll
             for (int r = 0; r < 32; ++r) {
                 const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
-                zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
+                if (!p.use_local) zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
                 const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
                 if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
             }

@@ -317,7 +317,7 @@ __device__ __forceinline__ float cta_sumsq_exact(int B, float* s_red, Get get)
     return __fadd_rn(lo, hi);
 }
 
-template <int T>
+template <int T, class Bar = CtaBar>
 __device__ __forceinline__ float cta_sumsq(const float* sm, int B, float* s_red)
 {
     float a = 0.f;
@@ -328,10 +328,10 @@ __device__ __forceinline__ float cta_sumsq(const float* sm, int B, float* s_red)
 #pragma unroll
     for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
     if (lane_id() == 0) s_red[warp_id()] = a;
-    __syncthreads();
+    Bar::sync();
     float t = 0.f;
     for (int w = 0; w < (T + 31) / 32; ++w) t += s_red[w];
-    __syncthreads();
+    Bar::sync();
     return t;
 }
 
@@ -860,8 +860,8 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
         CUtensorMap tmap;
         const int use_tma = make_volume_tmap(&tmap, d_vol, s.nx, s.ny, s.nz, 32, 32, 8) ? 1 : 0;
         long grid = ws->sm_count < s.nblk ? ws->sm_count : s.nblk;
-        if (!exact && !use_local && use_tma && ws_enabled()) {
-            // LIFTING, global RMS: warp-specialised kernel, the coder of block t overlaps the transform of block t+1
+        if (!exact && use_tma && ws_enabled()) {
+            // LIFTING: warp-specialised kernel, the coder of block t overlaps the transform of block t+1
             e = cudaFuncSetAttribute(k_encode32ws, cudaFuncAttributeMaxDynamicSharedMemorySize, E32_SMEM);
             if (e != cudaSuccess) return e;
             k_encode32ws<<<(unsigned)grid, E32_T, E32_SMEM, st>>>(tmap, p);

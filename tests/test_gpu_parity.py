@@ -506,3 +506,25 @@ def test_corrupted_payload_terminates(gpu, ws):
     finally:
         L.cvx_debug_set_ws(1)
         gpu.set_transform("exact")
+
+
+@pytest.mark.parametrize("case", [WS_CASES[0], WS_CASES[1], WS_CASES[2], WS_CASES[-3]], ids=lambda c: "%s-%dx%dx%d-b%dx%dx%d-s%g" % c)
+def test_warp_specialised_encoder_local_rms(gpu, case):
+    """Local RMS (CvxCompress.cpp:343-348) in LIFTING mode: k_encode32ws computes blkmulfac with the same 512-thread
+    reduction as k_encode32 -> identical streams (block multipliers included) and reconstructions."""
+    from cvxcompress_b200 import _lib
+    kind, nx, ny, nz, bx, by, bz, scale = case
+    vol = _vol(kind, nx, ny, nz)
+    L = _lib.lib()
+    gpu.set_transform("lifting")
+    try:
+        out = {}
+        for ws in (1, 0):
+            L.cvx_debug_set_ws(ws)
+            got, _ = _gpu_compress(gpu, vol, bx, by, bz, scale, True)
+            out[ws] = (got, _gpu_decompress(gpu, got, nx, ny, nz))
+    finally:
+        L.cvx_debug_set_ws(1)
+        gpu.set_transform("exact")
+    assert _streams_equal(out[1][0], out[0][0])
+    assert np.array_equal(out[1][1].view(np.uint32), out[0][1].view(np.uint32))
