@@ -16,11 +16,11 @@ constexpr int W32_TT = 512;                          // transform threads (warps
 constexpr int W32_PT = 256;                          // parser threads (warps 16..19)
 constexpr int W32_T = W32_TT + W32_PT;
 constexpr int W32_LCAP = 6144;                       // list entries (8 bytes each)
-constexpr int W32_OFF_WIN = F32_B * 4;               // parser window, then the in-line window
-constexpr int W32_OFF_EXT = W32_OFF_WIN + 2 * D32_WIN;
+constexpr int W32_OFF_WIN = F32_B * 4;               // two parser windows, then the in-line window
+constexpr int W32_OFF_EXT = W32_OFF_WIN + 3 * D32_WIN;
 constexpr int W32_OFF_MASK = W32_OFF_EXT + D32_CH * 4;          // uint8[1024] token-start masks of the parser
 constexpr int W32_OFF_LIST = W32_OFF_MASK + D32_CH;
-constexpr int W32_SMEM = W32_OFF_LIST + W32_LCAP * 8;           // 201 824 bytes
+constexpr int W32_SMEM = W32_OFF_LIST + W32_LCAP * 8;           // 210 048 bytes
 
 typedef NamedBar<1, W32_TT> TBar;                    // transform group
 typedef NamedBar<2, W32_PT> PBar;                    // parser group
@@ -179,31 +179,46 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         const int ptid = tid - W32_TT;
         int it = 0;
         W32_PH_DECL;
-        for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, ++it) {
-            const D32Src b = d32_locate(p, t);
-            const int entry = (int)(reinterpret_cast<uintptr_t>(b.src) & 15);
-            const bool servable = !b.raw && b.hint > 0 && entry + b.hint <= D32_CH * 8;
-            int n = -1;
-            if (servable) {
-                const uint8_t* cbase = b.src - entry;
+        // payload windows are double-buffered: the window of block t+1 is requested before block t is parsed
+        auto servable_of = [&](const D32Src& b) {
+            return !b.raw && b.hint > 0 && (int)(reinterpret_cast<uintptr_t>(b.src) & 15) + b.hint <= D32_CH * 8;
+        };
+        auto request = [&](const D32Src& b, unsigned char* w) {
+            if (servable_of(b)) {
+                const uint8_t* cbase = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(b.src) & ~(uintptr_t)15);
                 for (int g = ptid; g < D32_WIN / 16; g += W32_PT) {
                     const uint8_t* a = cbase + 16 * g;
                     long left = hi - a;
                     int nb = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
-                    cp_async16_zfill(s_win + 16 * g, nb > 0 ? a : cbase, nb);
+                    cp_async16_zfill(w + 16 * g, nb > 0 ? a : cbase, nb);
                 }
-                cp_async_commit();
-                cp_async_wait_all();
-                PBar::sync();
             }
+            cp_async_commit();                                     // one group per block, empty or not
+        };
+        D32Src b = d32_locate(p, blockIdx.x);
+        request(b, s_win);
+        for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, ++it) {
+            unsigned char* win = s_win + (it & 1) * D32_WIN;
+            D32Src bn = b;
+            if (t + gridDim.x < p.nblk) {
+                bn = d32_locate(p, t + gridDim.x);
+                request(bn, s_win + ((it + 1) & 1) * D32_WIN);     // that window's last reader finished before the previous PBar
+            } else {
+                cp_async_commit();
+            }
+            const bool servable = servable_of(b);
+            int n = -1;
+            asm volatile("cp.async.wait_group 1;" ::: "memory");   // this block's window has landed (this thread's part ...
+            PBar::sync();                                          // ... and everybody else's)
             W32_PH(6);
             if (it > 0) w32_wait(W32_BAR_EMPTY);                   // the previous list has been scattered
             W32_PH(7);
-            if (servable) n = w32_parse_to_list(b, s_win, s_mask, p_ext, pscratch64, s_list);
+            if (servable) n = w32_parse_to_list(b, win, s_mask, p_ext, pscratch64, s_list);
             if (ptid == 0) s_ctl[0] = n;
             __threadfence_block();
             PBar::sync();                                          // every parser thread is done with the window: the next load may overwrite it
             w32_arrive(W32_BAR_FULL);
+            b = bn;
             W32_PH(8);
         }
         W32_PH_FLUSH;
@@ -218,7 +233,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
 #pragma unroll
         for (int i = 0; i < F32_B / 4 / W32_TT; ++i) z4[tid + W32_TT * i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    unsigned char* win2 = s_win + D32_WIN;                          // window of the in-line path
+    unsigned char* win2 = s_win + 2 * D32_WIN;                      // window of the in-line path
     CVX_PH_DECL;
     for (long t = blockIdx.x; t < p.nblk; t += gridDim.x) {
         CVX_PH(5);

@@ -43,15 +43,27 @@
         }
         const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
         const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
+        if (!p.use_local) {              // coefficients back to the block buffer, one ballot per row
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {    // coefficients back to the block buffer, one ballot per row
-            float* zl = f32_zline(sm, tid + E32_TT * k);
+            for (int k = 0; k < 2; ++k) {
+                float* zl = f32_zline(sm, tid + E32_TT * k);
 #pragma unroll
-            for (int r = 0; r < 32; ++r) {
-                const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
-                if (!p.use_local) zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
-                const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
-                if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+                for (int r = 0; r < 32; ++r) {
+                    const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
+                    zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
+                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
+                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+                }
+            }
+        } else {                         // local RMS: the coefficients are already there
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
+                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
+                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+                }
             }
         }
         ETBar::sync();
