@@ -73,23 +73,37 @@ struct D32Src {
     float scalefac;
 };
 
-// table entry of block t -> where its payload is (CvxCompress.cpp:545-548) and, when the next entry is larger, how long
-__device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
+// table entry of block t -> where its payload is (CvxCompress.cpp:545-548) and, when the next entry is larger, how long.
+// Two steps so that a caller can issue the table loads a whole block ahead of their use (k_decode32ws parser).
+struct D32Raw {
+    unsigned long long o, o1;
+};
+__device__ __forceinline__ D32Raw d32_locate_issue(const DecParams& p, long t)
+{
+    D32Raw r;
+    r.o = 0; r.o1 = 0;
+    // volatile: issued where written, so the latency hides under whatever follows instead of in front of the first use
+    if (t < p.nblk) asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(r.o) : "l"(p.offs + t));
+    if (t + 1 < p.nblk) asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(r.o1) : "l"(p.offs + t + 1));
+    return r;
+}
+__device__ __forceinline__ D32Src d32_locate_finish(const DecParams& p, long t, const D32Raw& w)
 {
     D32Src r;
-    unsigned long long o, o1 = 0;
-    // volatile: issued where written (the loop top), so the latency hides under the parse instead of in front of the prefetch
-    asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(o) : "l"(p.offs + t));
-    if (t + 1 < p.nblk) asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(o1) : "l"(p.offs + t + 1));
+    unsigned long long o = w.o;
     r.raw = (int)(o >> 63);
     o &= 0x7FFFFFFFFFFFFFFFull;
     r.src = p.payload + o;
-    long nxt = (t + 1 < p.nblk) ? (long)(o1 & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
+    long nxt = (t + 1 < p.nblk) ? (long)(w.o1 & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
     long h = nxt - (long)o;
     r.hint = (h > 0 && h <= 5L * F32_B + 8) ? h : 0;
     const float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
     r.scalefac = __fdiv_rn(1.0f, mulfac);                        // Run_Length_Encode_Slow.cpp:392
     return r;
+}
+__device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
+{
+    return d32_locate_finish(p, t, d32_locate_issue(p, t));
 }
 
 // per-thread result of walking its two chunks of a window

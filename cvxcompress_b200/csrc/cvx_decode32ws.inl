@@ -197,15 +197,17 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         };
         D32Src b = d32_locate(p, blockIdx.x);
         request(b, s_win);
+        D32Raw nraw = d32_locate_issue(p, (long)blockIdx.x + gridDim.x);      // table entries are read one block ahead of their use
         for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, ++it) {
             unsigned char* win = s_win + (it & 1) * D32_WIN;
             D32Src bn = b;
             if (t + gridDim.x < p.nblk) {
-                bn = d32_locate(p, t + gridDim.x);
+                bn = d32_locate_finish(p, t + gridDim.x, nraw);
                 request(bn, s_win + ((it + 1) & 1) * D32_WIN);     // that window's last reader finished before the previous PBar
             } else {
                 cp_async_commit();
             }
+            nraw = d32_locate_issue(p, t + 2L * gridDim.x);
             const bool servable = servable_of(b);
             int n = -1;
             asm volatile("cp.async.wait_group 1;" ::: "memory");   // this block's window has landed (this thread's part ...
