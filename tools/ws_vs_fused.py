@@ -1,5 +1,6 @@
+"""Full-size check of the warp-specialised 32^3 kernels against the fused ones (LIFTING): repeated runs, device-side\ncomparison of streams and reconstructions; any difference is a race or a hand-over bug.  Run on a B200."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, numpy as np
 from cvxcompress_b200 import api, synth, _lib
 L = _lib.lib()
