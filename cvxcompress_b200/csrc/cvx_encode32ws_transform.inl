@@ -11,7 +11,8 @@
         if (t >= p.nblk) break;
         unsigned int nt = 0;
         if (tid == 0) nt = atomicAdd(p.ticket, 1u);            // the next block's ticket: round trip hidden under the transform
-        mbar_wait(&s_bar, parity);
+        mbar_wait(&s_bar[warp >> 3], parity);                  // the boxes holding z slices warp and warp + 16
+        mbar_wait(&s_bar[2 + (warp >> 3)], parity);
         parity ^= 1u;
         CVX_PH(0);
         f32_pass_x<EXACT, true>(sm);
