@@ -25,7 +25,7 @@ C_SYMBOLS = [
     "cvxgpu_sumsq_device", "cvxgpu_encode_blocks_device", "cvxgpu_write_header_device",
     "cvxgpu_offsets_add_device", "cvxgpu_decode_blocks_device", "cvxgpu_wavelet_blocks_device",
     "cvx_compress", "cvx_decompress_outofplace", "cvx_decompress_inplace", "cvx_compress_th",
-    "cvx_decompress_inplace_th",
+    "cvx_decompress_inplace_th", "cvxgpu_validate_stream",
 ]
 
 
@@ -33,6 +33,16 @@ class CvxError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("cvxgpu error %d: %s" % (code, msg))
         self.code = code
+
+
+class StreamInfo(C.Structure):
+    """cvxgpu_stream_info (include/cvx_gpu.h)."""
+    _fields_ = [(n, C.c_int) for n in ("nx", "ny", "nz", "bx", "by", "bz", "use_local_rms")] + [("glob_mulfac", C.c_float)] + \
+               [(n, C.c_long) for n in ("nblocks", "raw_blocks", "table_bytes", "payload_bytes", "used_payload_bytes",
+                                        "min_block_bytes", "max_block_bytes", "tokens")] + [("natural_order", C.c_int)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
 
 
 def build(force=False):
@@ -77,6 +87,7 @@ def lib():
     L.cvxgpu_compress_device_async.argtypes = [p, p, i, i, i, i, i, i, f, i, p, l, p, p, p]
     L.cvxgpu_decompress_device.argtypes = [p, p, i, i, i, p, l, p]
     L.cvxgpu_parse_header.argtypes = [p, l] + [C.POINTER(i)] * 6 + [C.POINTER(f), C.POINTER(i)]
+    L.cvxgpu_validate_stream.argtypes = [p, l, i, C.POINTER(StreamInfo)]
     L.cvxgpu_compress.argtypes = [p, i, i, i, i, i, i, f, i, p, C.POINTER(l), C.POINTER(f)]
     L.cvxgpu_decompress.argtypes = [p, i, i, i, p, l]
     L.cvxgpu_sumsq_device.argtypes = [p, p, l, p, p]

@@ -42,6 +42,19 @@ def parse_header(stream):
     return tuple(x.value for x in v) + (gm.value, fl.value)
 
 
+def validate_stream(stream, length=None, level=1):
+    """Bounds-checked walk of a HOST stream (numpy uint8 / bytes) before it is handed to a decoder: header, tables and,
+    at level 1, every token of every block (cvxgpu_validate_stream).  Returns the stream's facts as a dict; raises
+    CvxError (code CVXGPU_ERR_STREAM, message naming the first offending block) on a malformed stream.  No GPU needed."""
+    buf = np.frombuffer(bytes(stream), dtype=np.uint8) if not isinstance(stream, np.ndarray) else np.ascontiguousarray(stream).view(np.uint8).reshape(-1)
+    n = len(buf) if length is None else int(length)
+    if n > len(buf):
+        raise ValueError("length %d exceeds the %d-byte buffer" % (n, len(buf)))
+    info = _lib.StreamInfo()
+    _lib.check(_lib.lib().cvxgpu_validate_stream(buf.ctypes.data, n, int(level), C.byref(info)))
+    return info.as_dict()
+
+
 class CvxCompress:
     """Python mirror of the reference class for HOST buffers (numpy)."""
 

@@ -11,7 +11,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <mutex>
+#include <vector>
 
 using namespace cvx;
 
@@ -317,6 +319,120 @@ extern "C" int cvxgpu_parse_header(const void* h_stream, long length, int* nx, i
     if (bz) *bz = h[5];
     if (glob_mulfac) memcpy(glob_mulfac, &h[6], 4);
     if (flags) *flags = h[7];
+    return CVXGPU_OK;
+}
+
+// ---- stream validator (host memory, no GPU): SURVEY.md 8(f) row 3 -----------------------------
+// Token sizes and value counts of the reference's code table (Run_Length_Escape_Codes.hxx:8-14; decoder
+// Run_Length_Encode_Slow.cpp:416-512).  Returns the token's byte count and sets *nvals; needs p[0..3] readable
+// only as far as `avail` says.
+static inline int token_extent(const unsigned char* p, long avail, long* nvals)
+{
+    const int c = (signed char)p[0];
+    switch (c) {
+    case 127:  if (avail < 2) return 0; *nvals = p[1]; return 2;                                             // RLESC1
+    case 125:  if (avail < 4) return 0; *nvals = (long)p[1] | ((long)p[2] << 8) | ((long)p[3] << 16); return 4;  // RLESC3
+    case -125: *nvals = 1; return 3;   // VLESC2
+    case -127: *nvals = 1; return 4;   // VLESC3
+    case -128: *nvals = 1; return 5;   // VLESC4
+    case -126: *nvals = 8; return 17;  // VLESC2_8x
+    case 126:  *nvals = 8; return 25;  // VLESC3_8x
+    default:   *nvals = 1; return 1;   // literal -124..124
+    }
+}
+
+extern "C" int cvxgpu_validate_stream(const void* h_stream, long length, int level, cvxgpu_stream_info* info)
+{
+    cvxgpu_stream_info local_info;
+    cvxgpu_stream_info& I = info ? *info : local_info;
+    memset(&I, 0, sizeof(I));
+    I.used_payload_bytes = I.min_block_bytes = I.max_block_bytes = I.tokens = -1;
+    int flags;
+    int rc = cvxgpu_parse_header(h_stream, length, &I.nx, &I.ny, &I.nz, &I.bx, &I.by, &I.bz, &I.glob_mulfac, &flags);
+    if (rc) return rc;
+    I.use_local_rms = flags & 1;
+    if (flags & ~1) return fail(CVXGPU_ERR_STREAM, "header flags 0x%x: only bit 0 (local RMS) is defined", flags);
+    if (!std::isfinite(I.glob_mulfac) || I.glob_mulfac == 0.0f)
+        return fail(CVXGPU_ERR_STREAM, "global multiplier %g is not a finite non-zero number", (double)I.glob_mulfac);
+    const Shape s = make_shape(I.nx, I.ny, I.nz, I.bx, I.by, I.bz);
+    const long B = (long)I.bx * I.by * I.bz;
+    I.nblocks = s.nblk;
+    I.table_bytes = 8 * s.nblk + (I.use_local_rms ? 4 * s.nblk : 0);
+    I.payload_bytes = length - 32 - I.table_bytes - 7;      // CvxCompress.cpp:421-422: 7 bytes of slack end the stream
+    if (I.payload_bytes < 0)
+        return fail(CVXGPU_ERR_STREAM, "stream of %ld bytes cannot hold its header, %ld table bytes and the 7-byte slack",
+                    length, I.table_bytes);
+    const unsigned char* base = static_cast<const unsigned char*>(h_stream);
+    const unsigned char* payload = base + 32 + I.table_bytes;
+    const unsigned long long RAW = 1ULL << 63;
+    std::vector<unsigned long long> starts((size_t)s.nblk);
+    I.natural_order = 1;
+    unsigned long long prev = 0;
+    for (long b = 0; b < s.nblk; ++b) {
+        unsigned long long e;
+        memcpy(&e, base + 32 + 8 * b, 8);
+        const unsigned long long off = e & ~RAW;
+        if (off >= (unsigned long long)I.payload_bytes && !(off == 0 && I.payload_bytes == 0))
+            return fail(CVXGPU_ERR_STREAM, "block %ld: offset %llu lies outside the %ld payload bytes", b, off, I.payload_bytes);
+        if (e & RAW) {
+            ++I.raw_blocks;
+            if (off + 4ULL * B > (unsigned long long)I.payload_bytes)
+                return fail(CVXGPU_ERR_STREAM, "raw block %ld: %ld bytes at offset %llu pass the payload end %ld", b, 4 * B, off, I.payload_bytes);
+        }
+        if (b && off <= prev) I.natural_order = 0;
+        prev = off;
+        starts[(size_t)b] = off;
+        if (I.use_local_rms) {
+            float m;
+            memcpy(&m, base + 32 + 8 * s.nblk + 4 * b, 4);
+            if (!std::isfinite(m) || m == 0.0f)
+                return fail(CVXGPU_ERR_STREAM, "block %ld: multiplier %g is not a finite non-zero number", b, (double)m);
+        }
+    }
+    if (level <= 0) return CVXGPU_OK;
+
+    // every block must end at or before the next block's first byte (payload order is free: CvxCompress.cpp:382-384)
+    std::vector<unsigned long long> sorted(starts);
+    std::sort(sorted.begin(), sorted.end());
+    for (size_t i = 1; i < sorted.size(); ++i)
+        if (sorted[i] == sorted[i - 1])
+            return fail(CVXGPU_ERR_STREAM, "two blocks share payload offset %llu", sorted[i]);
+    I.used_payload_bytes = 0;
+    I.tokens = 0;
+    I.min_block_bytes = 1L << 62;
+    I.max_block_bytes = 0;
+    for (long b = 0; b < s.nblk; ++b) {
+        unsigned long long e;
+        memcpy(&e, base + 32 + 8 * b, 8);
+        const long off = (long)(e & ~RAW);
+        const auto nx = std::upper_bound(sorted.begin(), sorted.end(), (unsigned long long)off);
+        const long limit = nx == sorted.end() ? I.payload_bytes : (long)*nx;
+        long bytes;
+        if (e & RAW) {
+            bytes = 4 * B;
+        } else {
+            long pos = off, vals = 0;
+            while (vals < B) {
+                if (pos >= limit)
+                    return fail(CVXGPU_ERR_STREAM, "block %ld: %ld of %ld values decoded when its payload [%ld, %ld) ends", b, vals, B, (long)off, limit);
+                long nv = 0;
+                const int tb = token_extent(payload + pos, limit - pos, &nv);
+                if (tb == 0 || pos + tb > limit)
+                    return fail(CVXGPU_ERR_STREAM, "block %ld: token 0x%02x at payload byte %ld is cut off at %ld", b, payload[pos], pos, limit);
+                pos += tb;
+                vals += nv;
+                ++I.tokens;
+            }
+            if (vals != B)
+                return fail(CVXGPU_ERR_STREAM, "block %ld: tokens produce %ld values, the block holds %ld", b, vals, B);
+            bytes = pos - off;
+        }
+        if (off + bytes > limit)
+            return fail(CVXGPU_ERR_STREAM, "block %ld: %ld bytes at offset %ld run into the next block at %ld", b, bytes, (long)off, limit);
+        I.used_payload_bytes += bytes;
+        if (bytes < I.min_block_bytes) I.min_block_bytes = bytes;
+        if (bytes > I.max_block_bytes) I.max_block_bytes = bytes;
+    }
     return CVXGPU_OK;
 }
 

@@ -93,6 +93,33 @@ int cvxgpu_decompress_device(cvxgpu_workspace* ws, float* d_vol, int nx, int ny,
 int cvxgpu_parse_header(const void* h_stream, long length, int* nx, int* ny, int* nz,
                         int* bx, int* by, int* bz, float* glob_mulfac, int* flags);
 
+/* Bounds-checked walk of a stream held in HOST memory (no GPU needed): SURVEY.md 8(f) row 3.
+ * The reference decoder trusts the stream entirely (Run_Length_Encode_Slow.cpp:393-525 reads
+ * tokens until the block is full, wherever that leads) and never looks at compressed_length
+ * (CvxCompress.cpp:463-571); its authors left Compress_Safe/Decompress_Safe commented out
+ * (Test_With_Generated_Input.cpp:69-71,89).  This is that check, done before any byte is decoded:
+ *   level 0  header fields, length >= 32 + tables + 7, every table offset inside the payload,
+ *            a raw block's 4*B bytes inside the payload, finite non-zero multipliers;
+ *   level 1  additionally walks every coded block token by token: each token must lie inside the
+ *            payload, the values must add up to exactly B (a run may not overshoot the block),
+ *            and no block may run into the next block's first byte.
+ * Returns CVXGPU_OK or CVXGPU_ERR_STREAM (cvxgpu_last_error() names the first offending block);
+ * *info (may be NULL) is filled as far as the walk got. */
+typedef struct cvxgpu_stream_info {
+    int nx, ny, nz, bx, by, bz;
+    int use_local_rms;
+    float glob_mulfac;
+    long nblocks;
+    long raw_blocks;        /* table entries with bit 63 set                                  */
+    long table_bytes;       /* 8*nblocks (+ 4*nblocks with local RMS)                         */
+    long payload_bytes;     /* length - 32 - table_bytes - 7                                  */
+    long used_payload_bytes;/* level 1: sum of the block payloads the walk measured, else -1 */
+    long min_block_bytes, max_block_bytes; /* level 1, else -1                               */
+    long tokens;            /* level 1: tokens walked, else -1                               */
+    int natural_order;      /* 1 when table offsets increase with iBlk (num_threads=1 order) */
+} cvxgpu_stream_info;
+int cvxgpu_validate_stream(const void* h_stream, long length, int level, cvxgpu_stream_info* info);
+
 /* ---- host-pointer convenience (what the CvxCompress class calls) ---------------------------
  * `vol` / `stream` may be pageable host, pinned host, managed or device pointers
  * (cudaPointerGetAttributes); host memory is staged through pinned chunks. */
