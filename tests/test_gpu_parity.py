@@ -317,6 +317,10 @@ def test_full_size_config3_golden_length_and_roundtrip(gpu):
     assert ln2 == ln and torch.equal(s[:ln - 7], s2[:ln - 7])          # deterministic, natural block order
     offs = s[32:32 + 8 * 38610].view(torch.int64)
     assert bool((offs[1:] > offs[:-1]).all())                          # sorted offsets == natural order
+    # the host validator walks all 38610 blocks of the full-size stream and accounts for every payload byte
+    info = gpu.validate_stream(s[:ln].cpu().numpy())
+    assert info["nblocks"] == 38610 and info["natural_order"] == 1 and info["raw_blocks"] == 0
+    assert info["used_payload_bytes"] == info["payload_bytes"] == ln - 32 - 8 * 38610 - 7
 
 
 @pytest.mark.parametrize("world", [2, 3])
