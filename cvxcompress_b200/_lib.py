@@ -25,7 +25,7 @@ C_SYMBOLS = [
     "cvxgpu_sumsq_device", "cvxgpu_encode_blocks_device", "cvxgpu_write_header_device",
     "cvxgpu_offsets_add_device", "cvxgpu_decode_blocks_device", "cvxgpu_wavelet_blocks_device",
     "cvx_compress", "cvx_decompress_outofplace", "cvx_decompress_inplace", "cvx_compress_th",
-    "cvx_decompress_inplace_th", "cvxgpu_validate_stream",
+    "cvx_decompress_inplace_th", "cvxgpu_validate_stream", "cvxgpu_set_safe_decode", "cvxgpu_get_safe_decode",
 ]
 
 

@@ -55,6 +55,14 @@ def validate_stream(stream, length=None, level=1):
     return info.as_dict()
 
 
+def set_safe_decode(level):
+    """-1 / None: off (the reference's behaviour); 0 or 1: the host-pointer Decompress path validates a host stream at that
+    level before staging it (cvxgpu_set_safe_decode).  Returns the previous level."""
+    prev = _lib.lib().cvxgpu_get_safe_decode()
+    _lib.check(_lib.lib().cvxgpu_set_safe_decode(-1 if level is None else int(level)))
+    return prev
+
+
 class CvxCompress:
     """Python mirror of the reference class for HOST buffers (numpy)."""
 

@@ -63,6 +63,25 @@ extern "C" int cvxgpu_set_transform(int mode)
     g_transform.store(mode);
     return CVXGPU_OK;
 }
+// ---- safe decode: -1 off (reference behaviour: the stream is trusted), 0 / 1 = cvxgpu_validate_stream level run by
+// cvxgpu_decompress on HOST streams before they are staged.  Default from CVX_GPU_SAFE_DECODE ("0", "1"; unset = off).
+static std::atomic<int> g_safe_decode{-2};
+extern "C" int cvxgpu_get_safe_decode(void)
+{
+    int m = g_safe_decode.load();
+    if (m < -1) {
+        const char* e = getenv("CVX_GPU_SAFE_DECODE");
+        m = !e || !*e ? -1 : (!strcmp(e, "0") ? 0 : (!strcmp(e, "off") ? -1 : 1));
+        g_safe_decode.store(m);
+    }
+    return m;
+}
+extern "C" int cvxgpu_set_safe_decode(int level)
+{
+    if (level < -1 || level > 1) return fail(CVXGPU_ERR_ARG, "safe-decode level %d: use -1 (off), 0 or 1", level);
+    g_safe_decode.store(level);
+    return CVXGPU_OK;
+}
 static int exact_mode() { return cvxgpu_get_transform() == CVXGPU_TRANSFORM_EXACT ? 1 : 0; }
 
 // ---- workspace ------------------------------------------------------------------------------
@@ -572,6 +591,13 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
         // the reference never reads compressed_length (CvxCompress.cpp:463-571); callers may pass 0
         long len = length;
         if (len <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: compressed_length is required for host streams");
+        // opt-in Decompress_Safe (commented out in the reference, Test_With_Generated_Input.cpp:89): refuse a malformed
+        // host stream before a byte of it reaches the GPU
+        const int safe = cvxgpu_get_safe_decode();
+        if (safe >= 0) {
+            rc = cvxgpu_validate_stream(stream_in, len, safe, nullptr);
+            if (rc) return rc;
+        }
         rc = reserve(&ws->d_stage_stream, &ws->stage_stream_bytes, (size_t)len + 64);
         if (rc) return rc;
         rc = copy_chunked(ws->d_stage_stream, stream_in, (size_t)(len - 7 > 32 ? len - 7 : len), cudaMemcpyHostToDevice, st);

@@ -120,6 +120,16 @@ typedef struct cvxgpu_stream_info {
 } cvxgpu_stream_info;
 int cvxgpu_validate_stream(const void* h_stream, long length, int level, cvxgpu_stream_info* info);
 
+/* Opt-in safe decode for the host-pointer path (cvxgpu_decompress, hence CvxCompress::Decompress and
+ * cvx_decompress_*): level -1 = off, the reference's behaviour (default); 0 / 1 = run
+ * cvxgpu_validate_stream at that level on a HOST stream before it is staged to the GPU and return
+ * CVXGPU_ERR_STREAM instead of decoding (the class then reports and aborts like every other
+ * failure).  The initial level comes from the environment variable CVX_GPU_SAFE_DECODE ("0" or
+ * "1").  Device-resident streams are not walked: copy them to the host and call
+ * cvxgpu_validate_stream when they come from an untrusted source. */
+int cvxgpu_set_safe_decode(int level);
+int cvxgpu_get_safe_decode(void);
+
 /* ---- host-pointer convenience (what the CvxCompress class calls) ---------------------------
  * `vol` / `stream` may be pageable host, pinned host, managed or device pointers
  * (cudaPointerGetAttributes); host memory is staged through pinned chunks. */

@@ -148,3 +148,38 @@ def test_run_overshoot_and_cut_tokens_are_refused():
     b = good.copy(); b[pb + int(offs[1]) - 1] = 126
     with pytest.raises(_lib.CvxError, match="block 0"):
         api.validate_stream(b)
+
+
+def test_safe_decode_switch_is_host_logic():
+    L = _lib.lib()
+    prev = api.set_safe_decode(1)
+    try:
+        assert L.cvxgpu_get_safe_decode() == 1
+        assert api.set_safe_decode(None) == 1 and L.cvxgpu_get_safe_decode() == -1
+        assert L.cvxgpu_set_safe_decode(2) == _lib.ERR_ARG and b"safe-decode" in L.cvxgpu_last_error()
+        assert L.cvxgpu_get_safe_decode() == -1
+    finally:
+        api.set_safe_decode(prev)
+
+
+@pytest.mark.gpu
+def test_safe_decode_refuses_a_damaged_host_stream_before_the_gpu():
+    import ctypes as C
+    L = _lib.lib()
+    nx, ny, nz = 64, 64, 64
+    good, s = _good()
+    want = ol.oracle_decompress(good, nx, ny, nz)
+    bad = good.copy()
+    bad[s["payload_base"] + int(s["offs"][1] & np.uint64(0x7FFFFFFFFFFFFFFF)) - 1] = 126      # cut 25-byte token ends block 0
+    out = np.full(nx * ny * nz, 7.0, dtype=np.float32)
+    prev = api.set_safe_decode(1)
+    try:
+        rc = L.cvxgpu_decompress(out.ctypes.data, nx, ny, nz, bad.ctypes.data, len(bad))
+        assert rc == _lib.ERR_STREAM and b"block 0" in L.cvxgpu_last_error()
+        assert (out == 7.0).all()                                   # nothing was decoded
+        rc = L.cvxgpu_decompress(out.ctypes.data, nx, ny, nz, good.ctypes.data, len(good))
+        assert rc == 0 and np.array_equal(out.view(np.uint32), want.reshape(-1).view(np.uint32))
+        api.set_safe_decode(None)                                   # reference behaviour: decoded without a walk, and it terminates
+        assert L.cvxgpu_decompress(out.ctypes.data, nx, ny, nz, bad.ctypes.data, len(bad)) == 0
+    finally:
+        api.set_safe_decode(prev)
