@@ -183,3 +183,25 @@ def test_safe_decode_refuses_a_damaged_host_stream_before_the_gpu():
         assert L.cvxgpu_decompress(out.ctypes.data, nx, ny, nz, bad.ctypes.data, len(bad)) == 0
     finally:
         api.set_safe_decode(prev)
+
+
+def test_threaded_walk_equals_serial_walk(monkeypatch):
+    vol = _vol(160, 160, 96, seed=9)
+    stream, _ = ol.oracle_compress(vol, 8, 8, 8, 1e-3, False)          # 4800 blocks: enough for every host thread
+    monkeypatch.setenv("CVX_GPU_VALIDATE_THREADS", "1")
+    serial = api.validate_stream(stream)
+    monkeypatch.setenv("CVX_GPU_VALIDATE_THREADS", "7")
+    assert api.validate_stream(stream) == serial
+    monkeypatch.delenv("CVX_GPU_VALIDATE_THREADS")
+    assert api.validate_stream(stream) == serial
+    _facts_agree(serial, stream)
+    # two damaged blocks: the lowest one is reported whatever thread meets it first
+    s = ol.parse_stream(stream)
+    offs = (s["offs"] & np.uint64(0x7FFFFFFFFFFFFFFF)).astype(np.int64)
+    bad = stream.copy()
+    for blk in (4100, 1234):
+        bad[s["payload_base"] + int(offs[blk + 1]) - 1] = 126
+    for threads in ("1", "7", "64"):
+        monkeypatch.setenv("CVX_GPU_VALIDATE_THREADS", threads)
+        with pytest.raises(_lib.CvxError, match="block 1234:"):
+            api.validate_stream(bad)
