@@ -56,7 +56,7 @@ def test_ops_equal_the_oracle(dims, blk, scale, local):
 @pytest.mark.gpu
 def test_op_rejects_bad_block_size_and_wrong_dims():
     d = torch.zeros((16, 16, 16), device="cuda")
-    with pytest.raises(ValueError, match="invalid block size"):
+    with pytest.raises(ValueError, match="block size"):
         torch.ops.cvx.compress(d, 24, 8, 8, 1e-2, False)
     stream, _ = torch.ops.cvx.compress(d, 8, 8, 8, 1e-2, False)
     with pytest.raises(Exception, match="expects|holds"):
