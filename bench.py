@@ -220,7 +220,7 @@ def run_reference(args):
             "compress_mcells_s": info["compress_mcells_s"], "decompress_mcells_s": info["decompress_mcells_s"],
             "e2e": {"value": info["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, world):
@@ -517,14 +517,38 @@ def run_ours(args):
                 "gpu_launches_detail": "per step: k_sumsq, k_sumsq_finish, k_write_header, %s, k_finish_length "
                                        "(Compress) + %s (Decompress)" % (enc_name, dec_name),
                 "exact_mode": exact_info}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line (rank 0).  Libraries write there too (NCCL prints its "NCCL version ..." banner
+    on fd 1 when the box sets NCCL_DEBUG), so fd 1 is pointed at stderr for the life of the process and the result line
+    goes to a private duplicate of the original stdout."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
     args = parse_args()
+    _claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
