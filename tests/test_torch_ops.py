@@ -61,3 +61,31 @@ def test_op_rejects_bad_block_size_and_wrong_dims():
     stream, _ = torch.ops.cvx.compress(d, 8, 8, 8, 1e-2, False)
     with pytest.raises(Exception, match="expects|holds"):
         torch.ops.cvx.decompress(stream, 16, 16, 32)
+
+
+@pytest.mark.gpu
+def test_compress_op_replays_in_a_cuda_graph():
+    """Compress has no host synchronisation, so a small-volume checkpoint loop can be captured once and replayed
+    (six launches per call otherwise dominate small volumes)."""
+    api.set_transform("exact")
+    nx, ny, nz = 96, 64, 64
+    a = torch.from_numpy(synth.g2(nx, ny, nz)).cuda()
+    b = torch.from_numpy(synth.g2(nx, ny, nz)[::-1].copy()).cuda()
+    static_in = a.clone()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):                       # warm-up outside capture: workspace allocations happen here
+        for _ in range(2):
+            torch.ops.cvx.compress(static_in, 32, 32, 32, 1e-2, False)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        stream, length = torch.ops.cvx.compress(static_in, 32, 32, 32, 1e-2, False)
+    for vol in (a, b, a):
+        static_in.copy_(vol)
+        g.replay()
+        torch.cuda.synchronize()
+        want, _ = ol.oracle_compress(vol.cpu().numpy(), 32, 32, 32, 1e-2, False)
+        ln = int(length.item())
+        assert ln == len(want) and bytes(stream[:ln - 7].cpu().numpy()) == bytes(want[:-7])
