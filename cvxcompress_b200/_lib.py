@@ -26,6 +26,9 @@ C_SYMBOLS = [
     "cvxgpu_offsets_add_device", "cvxgpu_decode_blocks_device", "cvxgpu_wavelet_blocks_device",
     "cvx_compress", "cvx_decompress_outofplace", "cvx_decompress_inplace", "cvx_compress_th",
     "cvx_decompress_inplace_th", "cvxgpu_validate_stream", "cvxgpu_set_safe_decode", "cvxgpu_get_safe_decode",
+    "cvxgpu_workspace_release_thread_default", "cvxgpu_sumsq_rows_device", "cvxgpu_sum_rows_device",
+    "cvxgpu_shard_range", "cvxgpu_shard_unique_id", "cvxgpu_shard_create", "cvxgpu_shard_destroy",
+    "cvxgpu_compress_sharded", "cvxgpu_decompress_sharded", "cvxgpu_decompress_slab_device",
 ]
 
 
@@ -91,6 +94,16 @@ def lib():
     L.cvxgpu_compress.argtypes = [p, i, i, i, i, i, i, f, i, p, C.POINTER(l), C.POINTER(f)]
     L.cvxgpu_decompress.argtypes = [p, i, i, i, p, l]
     L.cvxgpu_sumsq_device.argtypes = [p, p, l, p, p]
+    L.cvxgpu_workspace_release_thread_default.argtypes = []
+    L.cvxgpu_sumsq_rows_device.argtypes = [p, p, l, i, i, p, p]
+    L.cvxgpu_sum_rows_device.argtypes = [p, i, p, p]
+    L.cvxgpu_shard_range.argtypes = [i, i, i, i] + [C.POINTER(i)] * 4
+    L.cvxgpu_shard_unique_id.argtypes = [p]
+    L.cvxgpu_shard_create.argtypes = [C.POINTER(p), p, p, i, i]
+    L.cvxgpu_shard_destroy.argtypes = [p]
+    L.cvxgpu_compress_sharded.argtypes = [p, p, i, i, i, i, i, i, f, i, p, p, p, p, l, p, p, p]
+    L.cvxgpu_decompress_sharded.argtypes = [p, p, i, i, i, i, i, i, i, p, p, p, p, p, p]
+    L.cvxgpu_decompress_slab_device.argtypes = [p, p, i, i, i, i, i, i, i, i, i, p, l, p]
     L.cvxgpu_encode_blocks_device.argtypes = [p, p, i, i, i, i, i, i, f, i, p, l, p, p, p, l, p, p, p]
     L.cvxgpu_write_header_device.argtypes = [p, i, i, i, i, i, i, f, i, p, l, p]
     L.cvxgpu_offsets_add_device.argtypes = [p, l, l, p]

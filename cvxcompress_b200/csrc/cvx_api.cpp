@@ -125,14 +125,19 @@ extern "C" int cvxgpu_workspace_destroy(cvxgpu_workspace* ws)
     if (ws->h_pinned) cudaFreeHost(ws->h_pinned);
     if (ws->d_stage_vol) cudaFree(ws->d_stage_vol);
     if (ws->d_stage_stream) cudaFree(ws->d_stage_stream);
-    if (ws->h_stage) cudaFreeHost(ws->h_stage);
+    if (ws->d_rowpartial) cudaFree(ws->d_rowpartial);
+    if (ws->d_rowsum) cudaFree(ws->d_rowsum);
     delete ws;
     return CVXGPU_OK;
 }
 
-// per-host-thread default workspaces, one per device
+// Per-host-thread default workspaces, one per (device, CUDA stream): the look-back status words, the ticket and the
+// scalar slab of a workspace belong to ONE call in flight, and two calls of one host thread on different streams may
+// overlap on the GPU (double-buffered checkpointing, a captured graph replayed next to eager work), so they must not
+// share them.  Calls on the same stream are ordered by the stream.  cvxgpu_workspace_release_thread_default() frees them.
 struct TlsWorkspaces {
-    cvxgpu_workspace* ws[64] = {nullptr};
+    struct Ent { int dev; cudaStream_t st; cvxgpu_workspace* ws; };
+    std::vector<Ent> v;
     ~TlsWorkspaces()
     {
         // the CUDA context may already be gone at thread/process exit: leak device memory, free nothing
@@ -140,19 +145,48 @@ struct TlsWorkspaces {
 };
 static thread_local TlsWorkspaces g_tls;
 
-static int get_ws(cvxgpu_workspace* in, cvxgpu_workspace** out)
+static int get_ws(cvxgpu_workspace* in, cvxgpu_workspace** out, void* cuda_stream)
 {
     if (in) { *out = in; return CVXGPU_OK; }
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64) return fail(CVXGPU_ERR_ARG, "device index %d out of range", dev);
-    if (!g_tls.ws[dev]) {
-        int rc = cvxgpu_workspace_create(&g_tls.ws[dev]);
-        if (rc != CVXGPU_OK) return rc;
-    }
-    *out = g_tls.ws[dev];
+    const cudaStream_t st = (cudaStream_t)cuda_stream;
+    for (auto& e : g_tls.v)
+        if (e.dev == dev && e.st == st) { *out = e.ws; return CVXGPU_OK; }
+    cvxgpu_workspace* ws = nullptr;
+    int rc = cvxgpu_workspace_create(&ws);
+    if (rc != CVXGPU_OK) return rc;
+    g_tls.v.push_back({dev, st, ws});
+    *out = ws;
     return CVXGPU_OK;
 }
+
+extern "C" int cvxgpu_workspace_release_thread_default(void)
+{
+    int rc = CVXGPU_OK;
+    for (auto& e : g_tls.v) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev != e.dev) cudaSetDevice(e.dev);
+        if (cudaDeviceSynchronize() != cudaSuccess) rc = CVXGPU_ERR_CUDA;
+        cvxgpu_workspace_destroy(e.ws);
+        if (dev != e.dev) cudaSetDevice(dev);
+    }
+    g_tls.v.clear();
+    return rc;
+}
+
+// for the other translation units of the library (cvx_shard.cpp)
+int cvx_internal_fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+int cvx_internal_exact_mode() { return exact_mode(); }
+int cvx_internal_default_ws(cvxgpu_workspace** out, void* cuda_stream) { return get_ws(nullptr, out, cuda_stream); }
 
 // ---- shape helpers --------------------------------------------------------------------------
 extern "C" int cvxgpu_is_valid_block_size(int bx, int by, int bz) { return valid_block_size(bx, by, bz) ? 1 : 0; }
@@ -182,10 +216,28 @@ static int check_dims(int nx, int ny, int nz, int bx, int by, int bz)
 extern "C" int cvxgpu_sumsq_device(cvxgpu_workspace* wsin, const float* d_vol, long ncells, double* d_sumsq, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     if (!d_vol || !d_sumsq || ncells <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_sumsq_device: bad argument");
     CU(launch_sumsq(ws, d_vol, ncells, d_sumsq, (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_sumsq_rows_device(cvxgpu_workspace* wsin, const float* d_vol, long plane_cells, int bz, int nz,
+                                        double* d_rowsums, void* cuda_stream)
+{
+    cvxgpu_workspace* ws;
+    int rc = get_ws(wsin, &ws, cuda_stream);
+    if (rc) return rc;
+    if (!d_vol || !d_rowsums || plane_cells <= 0 || bz <= 0 || nz <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_sumsq_rows_device: bad argument");
+    CU(launch_sumsq_rows(ws, d_vol, plane_cells, bz, nz, d_rowsums, (cudaStream_t)cuda_stream));
+    return CVXGPU_OK;
+}
+
+extern "C" int cvxgpu_sum_rows_device(const double* d_rowsums, int nrows, double* d_total, void* cuda_stream)
+{
+    if (!d_rowsums || !d_total || nrows < 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_sum_rows_device: bad argument");
+    CU(launch_sum_rows(d_rowsums, 0, 0, nullptr, nrows, d_total, (cudaStream_t)cuda_stream));
     return CVXGPU_OK;
 }
 
@@ -215,7 +267,7 @@ extern "C" int cvxgpu_encode_blocks_device(cvxgpu_workspace* wsin, const float* 
                                            long* d_payload_bytes, int* d_status, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     rc = check_dims(nx, ny, nz_slab, bx, by, bz);
     if (rc) return rc;
@@ -237,7 +289,7 @@ extern "C" int cvxgpu_decode_blocks_device(cvxgpu_workspace* wsin, float* d_vol_
                                            const void* d_payload, long payload_bytes, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     rc = check_dims(nx, ny, nz_slab, bx, by, bz);
     if (rc) return rc;
@@ -254,7 +306,7 @@ extern "C" int cvxgpu_wavelet_blocks_device(cvxgpu_workspace* wsin, float* d_blo
                                             int inverse, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     if (!valid_block_size(bx, by, bz)) return fail(CVXGPU_ERR_ARG, "invalid block size %d x %d x %d", bx, by, bz);
     if (!d_blocks || nblocks < 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_wavelet_blocks_device: bad argument");
@@ -275,7 +327,12 @@ static int compress_enqueue(cvxgpu_workspace* ws, const float* d_vol, const Shap
     unsigned char* d_payload = base + 32 + tables;                                          // :309 / :314
     const long ncells = (long)s.nx * s.ny * s.nz;
     CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
-    if (!local) CU(launch_sumsq(ws, d_vol, ncells, ws->d_sumsq, st));
+    if (!local) {
+        // per-block-row sums added in row order: the same arithmetic the sharded path performs for any number of GPUs
+        const int rows = s.nbz;
+        CU(launch_sumsq_rows(ws, d_vol, (long)s.nx * s.ny, s.bz, s.nz, nullptr, st));
+        CU(launch_sum_rows(ws->d_rowsum, 0, 0, nullptr, rows, ws->d_sumsq, st));
+    }
     CU(launch_write_header(d_stream, s, scale, local, ws->d_sumsq, ncells, ws->d_mulfac, st));
     CU(launch_encode(ws, d_vol, s, scale, local, ws->d_mulfac, d_offs, d_bmf, d_payload, capacity - 32 - tables - 7,
                      ws->d_payload_bytes, d_status, exact_mode(), st));
@@ -288,7 +345,7 @@ extern "C" int cvxgpu_compress_device_async(cvxgpu_workspace* wsin, const float*
                                             void* d_stream, long capacity, long* d_length, int* d_status, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     rc = check_dims(nx, ny, nz, bx, by, bz);
     if (rc) return rc;
@@ -302,7 +359,7 @@ extern "C" int cvxgpu_compress_device(cvxgpu_workspace* wsin, const float* d_vol
                                       void* d_stream, long capacity, long* length, float* ratio, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     rc = check_dims(nx, ny, nz, bx, by, bz);
     if (rc) return rc;
@@ -361,7 +418,21 @@ static inline int token_extent(const unsigned char* p, long avail, long* nvals)
     }
 }
 
+static int validate_stream_body(const void* h_stream, long length, int level, cvxgpu_stream_info* info);
+
 extern "C" int cvxgpu_validate_stream(const void* h_stream, long length, int level, cvxgpu_stream_info* info)
+{
+    // nothing may unwind through the C ABI: an allocation failure on a hostile header is a malformed stream
+    try {
+        return validate_stream_body(h_stream, length, level, info);
+    } catch (const std::exception& e) {
+        return fail(CVXGPU_ERR_STREAM, "stream validation aborted: %s", e.what());
+    } catch (...) {
+        return fail(CVXGPU_ERR_STREAM, "stream validation aborted");
+    }
+}
+
+static int validate_stream_body(const void* h_stream, long length, int level, cvxgpu_stream_info* info)
 {
     cvxgpu_stream_info local_info;
     cvxgpu_stream_info& I = info ? *info : local_info;
@@ -374,6 +445,14 @@ extern "C" int cvxgpu_validate_stream(const void* h_stream, long length, int lev
     if (flags & ~1) return fail(CVXGPU_ERR_STREAM, "header flags 0x%x: only bit 0 (local RMS) is defined", flags);
     if (!std::isfinite(I.glob_mulfac) || I.glob_mulfac == 0.0f)
         return fail(CVXGPU_ERR_STREAM, "global multiplier %g is not a finite non-zero number", (double)I.glob_mulfac);
+    // the header is untrusted: the block count is formed in 128 bits and must fit the stream before anything is sized by it
+    {
+        const long nbx = ((long)I.nx + I.bx - 1) / I.bx, nby = ((long)I.ny + I.by - 1) / I.by, nbz = ((long)I.nz + I.bz - 1) / I.bz;
+        const __int128 nnn = (__int128)nbx * nby * nbz;
+        const long room = length - 39;                          // header + 7 slack bytes
+        if (room < 0 || nnn > (__int128)(room / (I.use_local_rms ? 12 : 8)))
+            return fail(CVXGPU_ERR_STREAM, "stream of %ld bytes cannot hold the tables of the %ld x %ld x %ld blocks its header claims", length, nbx, nby, nbz);
+    }
     const Shape s = make_shape(I.nx, I.ny, I.nz, I.bx, I.by, I.bz);
     const long B = (long)I.bx * I.by * I.bz;
     I.nblocks = s.nblk;
@@ -479,6 +558,42 @@ extern "C" int cvxgpu_validate_stream(const void* h_stream, long length, int lev
     return CVXGPU_OK;
 }
 
+// The reference never reads compressed_length (CvxCompress.cpp:463-571), so a caller may pass 0 or garbage <= 0.  The
+// stream's extent follows from its own tables: the block with the largest payload offset ends the payload, a raw block
+// being 4*B bytes and a coded one as long as its tokens say (walked here, one block).  Host memory, header trusted as
+// the reference trusts it.
+static long derive_stream_length(const void* h_stream)
+{
+    int nx, ny, nz, bx, by, bz, flags;
+    if (cvxgpu_parse_header(h_stream, 32, &nx, &ny, &nz, &bx, &by, &bz, nullptr, &flags)) return -1;
+    const Shape s = make_shape(nx, ny, nz, bx, by, bz);
+    const long B = (long)bx * by * bz;
+    const long tables = 8 * s.nblk + ((flags & 1) ? 4 * s.nblk : 0);
+    const unsigned char* base = static_cast<const unsigned char*>(h_stream);
+    const unsigned long long RAW = 1ULL << 63;
+    unsigned long long best = 0;
+    bool best_raw = false;
+    for (long b = 0; b < s.nblk; ++b) {
+        unsigned long long e;
+        memcpy(&e, base + 32 + 8 * b, 8);
+        if ((e & ~RAW) >= best) { best = e & ~RAW; best_raw = (e & RAW) != 0; }
+    }
+    long bytes = 4 * B;
+    if (!best_raw) {
+        const unsigned char* p = base + 32 + tables + best;
+        long pos = 0, vals = 0;
+        while (vals < B) {
+            long nv = 0;
+            const int tb = token_extent(p + pos, 1L << 40, &nv);
+            pos += tb;
+            vals += nv;
+            if (pos > 5 * B + 64) return -1;
+        }
+        bytes = pos;
+    }
+    return 32 + tables + (long)best + bytes + 7;
+}
+
 static int decompress_with_header(cvxgpu_workspace* ws, float* d_vol, int nx, int ny, int nz, const int32_t* h,
                                   const void* d_stream, long length, cudaStream_t st)
 {
@@ -505,7 +620,7 @@ extern "C" int cvxgpu_decompress_device(cvxgpu_workspace* wsin, float* d_vol, in
                                         const void* d_stream, long length, void* cuda_stream)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(wsin, &ws);
+    int rc = get_ws(wsin, &ws, cuda_stream);
     if (rc) return rc;
     if (!d_vol || !d_stream) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress_device: null pointer");
     if (reinterpret_cast<uintptr_t>(d_stream) & 7) return fail(CVXGPU_ERR_ARG, "compressed stream must be 8-byte aligned");
@@ -551,7 +666,7 @@ extern "C" int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx,
                                int use_local_rms, void* stream_out, long* length, float* ratio)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(nullptr, &ws);
+    int rc = get_ws(nullptr, &ws, nullptr);
     if (rc) return rc;
     rc = check_dims(nx, ny, nz, bx, by, bz);
     if (rc) return rc;
@@ -595,7 +710,7 @@ extern "C" int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx,
 extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void* stream_in, long length)
 {
     cvxgpu_workspace* ws;
-    int rc = get_ws(nullptr, &ws);
+    int rc = get_ws(nullptr, &ws, nullptr);
     if (rc) return rc;
     if (!vol || !stream_in) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: null pointer");
     const int vol_dev = pointer_on_device(vol), in_dev = pointer_on_device(stream_in);
@@ -603,6 +718,7 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
     if (in_dev && vol_dev) return cvxgpu_decompress_device(ws, vol, nx, ny, nz, stream_in, length, st);
     int32_t h[8];
     if (in_dev) {
+        if (reinterpret_cast<uintptr_t>(stream_in) & 7) return fail(CVXGPU_ERR_ARG, "compressed stream must be 8-byte aligned");
         CU(cudaMemcpy(h, stream_in, 32, cudaMemcpyDeviceToHost));
     } else {
         memcpy(h, stream_in, 32);
@@ -614,7 +730,11 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
     if (!in_dev) {
         // the reference never reads compressed_length (CvxCompress.cpp:463-571); callers may pass 0
         long len = length;
-        if (len <= 0) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: compressed_length is required for host streams");
+        if (len <= 0) {
+            len = derive_stream_length(stream_in);
+            if (len <= 0) return fail(CVXGPU_ERR_STREAM, "cvxgpu_decompress: cannot derive the stream length from its tables");
+            length = len;
+        }
         // opt-in Decompress_Safe (commented out in the reference, Test_With_Generated_Input.cpp:89): refuse a malformed
         // host stream before a byte of it reaches the GPU
         const int safe = cvxgpu_get_safe_decode();

@@ -219,8 +219,9 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
 }
 
 template <bool EXACT, int T>
-__global__ void __launch_bounds__(T, 1) k_decode32(const DecParams p)
+__global__ void __launch_bounds__(T, 1) k_decode32(const DecParams pin)
 {
+    const DecParams p = dec_resolve(pin);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     unsigned char* s_win = smem_raw + D32_OFF_WIN;

@@ -155,8 +155,9 @@ __device__ __forceinline__ int w32_parse_to_list(const D32Src& b, const unsigned
     return (int)tote;
 }
 
-__global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
+__global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
 {
+    const DecParams p = dec_resolve(pin);
     constexpr bool EXACT = false;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         TBar::sync();                                               // block complete, s_ctl and the list consumed
         w32_arrive(W32_BAR_EMPTY);
         CVX_PH(1);
-        f32_pass_xT<EXACT, false, W32_TT>(sm);
+        f32_pass_xT<EXACT, false, W32_TT>(sm, true);
         __syncwarp();
         f32_pass_yT<EXACT, false, W32_TT>(sm);
         TBar::sync();
@@ -284,11 +285,13 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
         typename LineOf<EXACT, W32_TT>::type v[32];
         {
             float* zl = f32_zline(sm, tid);
+            if (warp >= 8) asm volatile("bar.sync 7, 512;" ::: "memory");       // skew: see f32_pass_x
 #pragma unroll
             for (int r = 0; r < 32; ++r) {
                 float* e = zl + reg_to_sub<32, EXACT>(r) * 1024;
                 p_set(v[r], e[0], e[512]);
             }
+            if (warp < 8) asm volatile("bar.arrive 7, 512;" ::: "memory");
 #pragma unroll
             for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
         }
@@ -304,7 +307,13 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams p)
             const int gy = iiy * 32 + warp + 16 * k;
             if (gx < p.g.nx && gy < p.g.ny) {
                 float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
-                if (nzl == 32) {
+                if (nzl == 32 && plane < (1L << 30)) {
+                    // plane j of the block: one 32 x 32 -> 64 bit multiply-add per row store (IMAD.WIDE) instead of a carried 64-bit add
+                    const unsigned pb = (unsigned)plane * 4u;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        *reinterpret_cast<float*>(reinterpret_cast<char*>(dp) + (unsigned long long)pb * (unsigned)j) = k ? p_hi(v[j]) : p_lo(v[j]);
+                } else if (nzl == 32) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) { *dp = k ? p_hi(v[j]) : p_lo(v[j]); dp += plane; }
                 } else {

@@ -23,9 +23,11 @@
         CVX_PH(2);
         typename PairOf<EXACT>::type vz[32];                   // z lines in registers: (x = lane, y = warp + 16 k)
         {
+            if (warp >= 8) asm volatile("bar.sync 7, 512;" ::: "memory");      // second half starts its loads when the first half's are issued
             const float* zl = f32_zline(sm, tid);
 #pragma unroll
             for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
+            if (warp < 8) asm volatile("bar.arrive 7, 512;" ::: "memory");
             fwd_line<32, EXACT>(vz);
         }
         float mulfac = gmul;

@@ -88,8 +88,10 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 // element (x, y, z) lives at float index  z*1024 + y*32 + (x ^ ((y & 7) << 2))
 
 // x lines: the thread's row is 8 chunks of 16 bytes; logical chunk c sits at physical chunk c ^ (row & 7)
+// `skew`: the two halves of a 512-thread group enter the pass one after the other (named barrier 7: the second half
+// starts its loads when the first half's are issued), so that one half's shared-memory phase overlaps the other's math
 template <bool EXACT, bool FWD>
-__device__ __forceinline__ void f32_pass_x(float* sm)
+__device__ __forceinline__ void f32_pass_x(float* sm, const bool skew = false)
 {
     // both rows of the thread (r = tid and tid + 512) in one straight-line block: the two independent dependency
     // chains interleave and fill the FMA pipe where one row's deep (short) levels would leave bubbles
@@ -97,6 +99,7 @@ __device__ __forceinline__ void f32_pass_x(float* sm)
     float4* row1 = row0 + (F32_T * 32) / 4;
     const int k = threadIdx.x & 7;                 // (tid + 512) & 7 == tid & 7: same swizzle for both rows
     float v[2][32];
+    if (skew && (threadIdx.x & 256)) asm volatile("bar.sync 7, 512;" ::: "memory");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         float4* row = h ? row1 : row0;
@@ -111,8 +114,17 @@ __device__ __forceinline__ void f32_pass_x(float* sm)
             }
         }
     }
-    if (FWD) { fwd_line<32, EXACT>(v[0]); fwd_line<32, EXACT>(v[1]); }
-    else { inv_line<32, EXACT>(v[0]); inv_line<32, EXACT>(v[1]); }
+    if (skew && !(threadIdx.x & 256)) asm volatile("bar.arrive 7, 512;" ::: "memory");
+    if constexpr (EXACT) {
+        if (FWD) { fwd_line<32, EXACT>(v[0]); fwd_line<32, EXACT>(v[1]); }
+        else { inv_line<32, EXACT>(v[0]); inv_line<32, EXACT>(v[1]); }
+    } else {
+        // LIFTING: the two rows run side by side in packed registers between their first and last scalar operation
+        float w[2][32];
+        if (FWD) fwd_lift_pair<32>(v[0], v[1], w[0], w[1]); else inv_lift_pair<32>(v[0], v[1], w[0], w[1]);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { v[0][i] = w[0][i]; v[1][i] = w[1][i]; }
+    }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         float4* row = h ? row1 : row0;
@@ -193,10 +205,10 @@ __device__ __forceinline__ void f32_pass_y2(float* sm)
 // ---- thread-count generic passes: T = 512 (two lines per thread) or 1024 (one line per thread, 64-register budget,
 //      twice the warps to hide latencies; LIFTING only -- the EXACT level copy does not fit 64 registers) ----
 template <bool EXACT, bool FWD, int T>
-__device__ __forceinline__ void f32_pass_xT(float* sm)
+__device__ __forceinline__ void f32_pass_xT(float* sm, const bool skew = false)
 {
     if constexpr (T == 512) {
-        f32_pass_x<EXACT, FWD>(sm);
+        f32_pass_x<EXACT, FWD>(sm, skew);
     } else {
         float4* row = reinterpret_cast<float4*>(sm + threadIdx.x * 32);
         const int k = threadIdx.x & 7;

@@ -18,6 +18,9 @@ struct cvxgpu_workspace {
     int* d_err = nullptr;
     double* d_partial = nullptr;          // per-CTA partial sums of k_sumsq
     int n_partial = 0;
+    double* d_rowpartial = nullptr;       // per-CTA partial sums of k_sumsq_rows (64 per block row)
+    double* d_rowsum = nullptr;           // one sum of squares per block row
+    int rows_cap = 0;
     unsigned long long* d_status = nullptr;   // look-back words
     long status_cap = 0;
     float* d_scratch = nullptr;           // staged path: dense coefficient blocks
@@ -29,9 +32,9 @@ struct cvxgpu_workspace {
     size_t stage_vol_bytes = 0;
     unsigned char* d_stage_stream = nullptr;
     size_t stage_stream_bytes = 0;
-    unsigned char* h_stage = nullptr;     // pinned bounce buffer
-    size_t h_stage_bytes = 0;
 };
+
+int cvx_internal_default_ws(cvxgpu_workspace** out, void* cuda_stream);
 
 namespace cvx {
 
@@ -50,6 +53,9 @@ cudaError_t ws_reserve_status(cvxgpu_workspace* ws, long nblk);
 cudaError_t ws_reserve_scratch(cvxgpu_workspace* ws, size_t bytes);
 
 cudaError_t launch_sumsq(cvxgpu_workspace* ws, const float* d_vol, long ncells, double* d_sumsq, cudaStream_t st);
+cudaError_t ws_reserve_rows(cvxgpu_workspace* ws, int rows);
+cudaError_t launch_sumsq_rows(cvxgpu_workspace* ws, const float* d_vol, long plane_cells, int bz, int nz, double* d_rowsum, cudaStream_t st);
+cudaError_t launch_sum_rows(const double* d_rows, int nseg, int seg, const int* d_cnt, int n_single, double* d_total, cudaStream_t st);
 cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int use_local, const double* d_sumsq,
                                 long ncells_total, float* d_mulfac_out, cudaStream_t st);
 cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape& s, float scale, int use_local,
@@ -59,7 +65,10 @@ cudaError_t launch_finish_length(const long* d_payload_bytes, long table_bytes, 
 cudaError_t launch_offsets_add(unsigned long long* d_offs, long n, long base, cudaStream_t st);
 cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, float glob_mulfac, int use_local,
                           const unsigned long long* d_offs, const float* d_blkmulfac, const void* d_payload,
-                          long payload_bytes, int exact, cudaStream_t st);
+                          long payload_bytes, int exact, cudaStream_t st, const float* d_glob_mulfac = nullptr,
+                          const long* d_payload_bytes = nullptr, const long* d_offs_bias = nullptr);
+cudaError_t launch_shard_fixup(const long* d_sizes, int world, int rank, long* d_bases, unsigned long long* d_offs, long n, cudaStream_t st);
+cudaError_t launch_shard_extent(const long* d_bases, int rank, long* d_out2, cudaStream_t st);
 cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, int bx, int by, int bz, int inverse,
                            int exact, cudaStream_t st);
 

@@ -74,6 +74,78 @@ __global__ void k_sumsq_finish(const double* __restrict__ partial, int n, double
     if (threadIdx.x == 0) *out = s;
 }
 
+// ---- the same reduction, per block row (z range of one row of blocks), independent of how the volume is cut into
+// slabs: the global RMS of a volume sharded over G GPUs must not depend on G, so every block row's sum
+// is formed by a fixed number of CTAs in a fixed order relative to the ROW start (no alignment peel: rows that do not
+// start on a 16-byte boundary take scalar loads into the same four accumulators), and the rows are added in row order.
+constexpr int SUMSQ_ROW_CTAS = 64;
+
+__global__ void __launch_bounds__(SUMSQ_T) k_sumsq_rows(const float* __restrict__ vol, long plane_cells, int bz, int nz,
+                                                        double* __restrict__ partial)
+{
+    const int row = blockIdx.y;
+    const int z0 = row * bz;
+    const int nzr = min(bz, nz - z0);
+    const long n = plane_cells * nzr;
+    const float* base = vol + plane_cells * (long)z0;
+    const long nthreads = (long)SUMSQ_ROW_CTAS * SUMSQ_T;
+    const long gtid = (long)blockIdx.x * SUMSQ_T + threadIdx.x;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    const long n4 = n >> 2;
+    if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+        const float4* v4 = reinterpret_cast<const float4*>(base);
+        for (long i = gtid; i < n4; i += nthreads) {
+            const float4 q = __ldg(&v4[i]);
+            const double d0 = q.x, d1 = q.y, d2 = q.z, d3 = q.w;
+            a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
+        }
+    } else {
+        for (long i = gtid; i < n4; i += nthreads) {
+            const double d0 = __ldg(base + 4 * i), d1 = __ldg(base + 4 * i + 1), d2 = __ldg(base + 4 * i + 2), d3 = __ldg(base + 4 * i + 3);
+            a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
+        }
+    }
+    if (gtid < n - (n4 << 2)) { const double d = base[(n4 << 2) + gtid]; a0 += d * d; }
+    double s = (a0 + a1) + (a2 + a3);
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    __shared__ double sw[SUMSQ_T / 32];
+    if (lane_id() == 0) sw[warp_id()] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < SUMSQ_T / 32; ++w) t += sw[w];
+        partial[(long)row * SUMSQ_ROW_CTAS + blockIdx.x] = t;
+    }
+}
+
+// one warp per block row: its SUMSQ_ROW_CTAS partials in a fixed order
+__global__ void k_sumsq_rows_finish(const double* __restrict__ partial, double* __restrict__ rowsum)
+{
+    const int row = blockIdx.x;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < SUMSQ_ROW_CTAS; i += 32) s += partial[(long)row * SUMSQ_ROW_CTAS + i];
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if (threadIdx.x == 0) rowsum[row] = s;
+}
+
+// total = rows added one after the other in row order.  `rows` may be the concatenation of per-rank segments of
+// `seg` doubles each (the receive buffer of an all-gather): rank r contributes its first cnt[r] entries.
+__global__ void k_sum_rows(const double* __restrict__ rows, int nseg, int seg, const int* __restrict__ cnt, int n_single,
+                           double* __restrict__ total)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double s = 0.0;
+    if (nseg <= 0) {
+        for (int i = 0; i < n_single; ++i) s += rows[i];
+    } else {
+        for (int r = 0; r < nseg; ++r)
+            for (int i = 0; i < cnt[r]; ++i) s += rows[(long)r * seg + i];
+    }
+    *total = s;
+}
+
 // glob_mulfac = 1 / (rms * scale), 1 when rms == 0 or the result is not finite (CvxCompress.cpp:291-295);
 // rms = (float)sqrt(sumsq / N) (:115-116).  With local RMS the global rms is taken as 1 (:249).
 __device__ __forceinline__ float glob_mulfac_of(const double* sumsq, long ncells, float scale, int use_local)
@@ -103,6 +175,28 @@ __global__ void k_offsets_add(unsigned long long* offs, long n, unsigned long lo
 {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) offs[i] += base;          // bit 63 (raw flag) is untouched: base < 2^63
+}
+
+// z-slab sharding: sizes[r] = payload bytes of rank r (all-gathered).  bases = exclusive prefix
+// (bases[world] = total payload), and this rank's table slice becomes global by adding bases[rank] (bit 63, the raw
+// flag, is untouched: the sum stays below 2^63).
+__global__ void k_shard_fixup(const long* __restrict__ sizes, int world, int rank, long* __restrict__ bases,
+                              unsigned long long* __restrict__ offs, long n)
+{
+    long base = 0;
+    for (int r = 0; r < rank; ++r) base += sizes[r];
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) offs[i] += (unsigned long long)base;
+    if (i == 0) {
+        long acc = 0;
+        for (int r = 0; r < world; ++r) { bases[r] = acc; acc += sizes[r]; }
+        bases[world] = acc;
+    }
+}
+// out[0] = bases[rank + 1] - bases[rank] (this rank's payload bytes), out[1] = bases[rank]
+__global__ void k_shard_extent(const long* __restrict__ bases, int rank, long* __restrict__ out)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) { out[0] = bases[rank + 1] - bases[rank]; out[1] = bases[rank]; }
 }
 
 // length = 32 + 8*nnn [+ 4*nnn] + payload + 7  (CvxCompress.cpp:421-422)
@@ -466,7 +560,20 @@ struct DecParams {
     const float* blkmulfac;
     const uint8_t* payload;
     long payload_bytes;
+    // when non-null these device scalars replace the two by-value fields above (a decode enqueued behind the encode that
+    // produces them: no host round trip, CUDA-graph capturable)
+    const float* gm_ptr;
+    const long* pbytes_ptr;
+    const long* bias_ptr;            // table offsets are biased by *bias_ptr (a rank's slice of a sharded stream: global offsets)
 };
+__device__ __forceinline__ DecParams dec_resolve(const DecParams& in)
+{
+    DecParams p = in;
+    if (in.gm_ptr) p.glob_mulfac = *in.gm_ptr;
+    if (in.pbytes_ptr) p.payload_bytes = *in.pbytes_ptr;
+    if (in.bias_ptr) { const long b = *in.bias_ptr; p.payload -= b; p.payload_bytes += b; }
+    return p;
+}
 
 template <int T, class PutV, class Phys>
 __device__ __forceinline__ void decode_head(const DecParams& p, long t, float* coef, PutV put, Phys phys,
@@ -502,8 +609,9 @@ __device__ __forceinline__ void decode_head(const DecParams& p, long t, float* c
 }
 
 template <int MAXN, bool EXACT, int T, int MINB>
-__global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams p)
+__global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams pin)
 {
+    const DecParams p = dec_resolve(pin);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     uint32_t* s_win = reinterpret_cast<uint32_t*>(smem_raw + (size_t)p.s.B * 4);
@@ -649,8 +757,9 @@ __global__ void __launch_bounds__(STAGE_T, 1) k_stage_encode(const EncParams p, 
     }
 }
 
-__global__ void __launch_bounds__(STAGE_T, 1) k_stage_decode(const DecParams p, float* scratch, long blk_first, int nb)
+__global__ void __launch_bounds__(STAGE_T, 1) k_stage_decode(const DecParams pin, float* scratch, long blk_first, int nb)
 {
+    const DecParams p = dec_resolve(pin);
     __shared__ uint32_t s_win[(STAGE_T + 2) * 4];
     __shared__ int s_ext[STAGE_T];
     __shared__ int scratch_i[72];
@@ -686,7 +795,7 @@ Shape make_shape(int nx, int ny, int nz, int bx, int by, int bz)
 {
     Shape s;
     s.nx = nx; s.ny = ny; s.nz = nz; s.bx = bx; s.by = by; s.bz = bz;
-    s.nbx = (nx + bx - 1) / bx; s.nby = (ny + by - 1) / by; s.nbz = (nz + bz - 1) / bz;
+    s.nbx = (int)(((long)nx + bx - 1) / bx); s.nby = (int)(((long)ny + by - 1) / by); s.nbz = (int)(((long)nz + bz - 1) / bz);
     s.nblk = (long)s.nbx * s.nby * s.nbz;
     return s;
 }
@@ -772,6 +881,45 @@ cudaError_t launch_sumsq(cvxgpu_workspace* ws, const float* d_vol, long ncells, 
     return cudaGetLastError();
 }
 
+cudaError_t ws_reserve_rows(cvxgpu_workspace* ws, int rows)
+{
+    if (rows <= ws->rows_cap) return cudaSuccess;
+    if (ws->d_rowpartial) cudaFree(ws->d_rowpartial);
+    if (ws->d_rowsum) cudaFree(ws->d_rowsum);
+    ws->d_rowpartial = nullptr; ws->d_rowsum = nullptr; ws->rows_cap = 0;
+    const int cap = rows + 64;
+    cudaError_t e = cudaMalloc(&ws->d_rowpartial, sizeof(double) * (size_t)cap * SUMSQ_ROW_CTAS);
+    if (e != cudaSuccess) return e;
+    e = cudaMalloc(&ws->d_rowsum, sizeof(double) * (size_t)cap);
+    if (e != cudaSuccess) return e;
+    ws->rows_cap = cap;
+    return cudaSuccess;
+}
+
+// per-block-row sums of squares of a volume or z-slab that starts on a block-row boundary: d_rowsum[(nz + bz - 1) / bz]
+cudaError_t launch_sumsq_rows(cvxgpu_workspace* ws, const float* d_vol, long plane_cells, int bz, int nz, double* d_rowsum,
+                              cudaStream_t st)
+{
+    const int rows = (nz + bz - 1) / bz;
+    cudaError_t e = ws_reserve_rows(ws, rows);
+    if (e != cudaSuccess) return e;
+    if (!d_rowsum) d_rowsum = ws->d_rowsum;
+    for (int r0 = 0; r0 < rows; r0 += 32768) {         // gridDim.y limit
+        const int nr = rows - r0 < 32768 ? rows - r0 : 32768;
+        k_sumsq_rows<<<dim3(SUMSQ_ROW_CTAS, nr), SUMSQ_T, 0, st>>>(d_vol + plane_cells * (long)bz * r0, plane_cells, bz, nz - r0 * bz,
+                                                                    ws->d_rowpartial + (long)r0 * SUMSQ_ROW_CTAS);
+    }
+    k_sumsq_rows_finish<<<rows, 32, 0, st>>>(ws->d_rowpartial, d_rowsum);
+    return cudaGetLastError();
+}
+
+// d_total = rows in order; with nseg > 0 `d_rows` is nseg segments of `seg` doubles of which the first d_cnt[r] count
+cudaError_t launch_sum_rows(const double* d_rows, int nseg, int seg, const int* d_cnt, int n_single, double* d_total, cudaStream_t st)
+{
+    k_sum_rows<<<1, 32, 0, st>>>(d_rows, nseg, seg, d_cnt, n_single, d_total);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int use_local, const double* d_sumsq,
                                 long ncells_total, float* d_mulfac_out, cudaStream_t st)
 {
@@ -783,6 +931,18 @@ cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int
 cudaError_t launch_finish_length(const long* d_payload_bytes, long table_bytes, long* d_length, cudaStream_t st)
 {
     k_finish_length<<<1, 32, 0, st>>>(d_payload_bytes, table_bytes, d_length);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shard_fixup(const long* d_sizes, int world, int rank, long* d_bases, unsigned long long* d_offs, long n, cudaStream_t st)
+{
+    const long nn = n > 0 ? n : 1;
+    k_shard_fixup<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(d_sizes, world, rank, d_bases, d_offs, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_shard_extent(const long* d_bases, int rank, long* d_out2, cudaStream_t st)
+{
+    k_shard_extent<<<1, 32, 0, st>>>(d_bases, rank, d_out2);
     return cudaGetLastError();
 }
 
@@ -912,9 +1072,11 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
 
 cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, float glob_mulfac, int use_local,
                           const unsigned long long* d_offs, const float* d_blkmulfac, const void* d_payload,
-                          long payload_bytes, int exact, cudaStream_t st)
+                          long payload_bytes, int exact, cudaStream_t st, const float* d_glob_mulfac, const long* d_payload_bytes,
+                          const long* d_offs_bias)
 {
     DecParams p;
+    p.gm_ptr = d_glob_mulfac; p.pbytes_ptr = d_payload_bytes; p.bias_ptr = d_offs_bias;
     p.vol = d_vol; p.g = vol_view(s, d_vol); p.s = blk_shape(s); p.nbx = s.nbx; p.nby = s.nby; p.nblk = s.nblk;
     p.glob_mulfac = glob_mulfac; p.use_local = use_local; p.offs = d_offs; p.blkmulfac = d_blkmulfac;
     p.payload = reinterpret_cast<const uint8_t*>(d_payload); p.payload_bytes = payload_bytes;

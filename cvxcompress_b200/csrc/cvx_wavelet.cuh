@@ -341,6 +341,77 @@ CVX_HD void inv_lift(V* v)
     inv_lift_levels<N, 1>(v);
 }
 
+// Two lines that arrive and leave as SCALARS (the x rows of a block come out of LDS.128 quads, whose registers cannot be
+// addressed as packed pairs): the pair (line a, line b) is formed by the first scalar operation that touches a sample
+// and split again by the last one, so everything in between runs packed (FADD2/FFMA2) without a single register move.
+// Same operations in the same order as fwd_lift / inv_lift on each line: bit-identical results.
+//   forward: level-1 steps 1 and 2 write the packed d and s; the final scaling (scalar) unpacks.   560 -> 360 issue slots
+//   inverse: the scaling packs; level-1 steps 3 and 4 (scalar) unpack.
+template <int N, int P>
+CVX_HD void lift_unpack_scale_fwd(const F2* v, float* oa, float* ob)
+{
+    constexpr float c = lift_scale_fwd(P, N);
+    oa[P] = CVX_MUL(c, f2_lo(v[P]));
+    ob[P] = CVX_MUL(c, f2_hi(v[P]));
+    if constexpr (P + 1 < N) lift_unpack_scale_fwd<N, P + 1>(v, oa, ob);
+}
+template <int N, int P>
+CVX_HD void lift_pack_scale_inv(const float* a, const float* b, F2* v)
+{
+    constexpr float c = lift_scale_inv(P, N);
+    v[P] = f2_make(CVX_MUL(c, a[P]), CVX_MUL(c, b[P]));
+    if constexpr (P + 1 < N) lift_pack_scale_inv<N, P + 1>(a, b, v);
+}
+// a, b: natural order in; oa, ob: interleaved (lifting) positions out
+template <int N>
+CVX_HD void fwd_lift_pair(const float* a, const float* b, float* oa, float* ob)
+{
+    constexpr int m = N / 2;
+    F2 v[N];
+#pragma unroll
+    for (int j = 0; j < m; ++j) {
+        const int jn = j + 1 < m ? j + 1 : m - 1;
+        v[2 * j + 1] = f2_make(CVX_FMA(CVX_LA, CVX_ADD(a[2 * j], a[2 * jn]), a[2 * j + 1]),
+                               CVX_FMA(CVX_LA, CVX_ADD(b[2 * j], b[2 * jn]), b[2 * j + 1]));
+    }
+#pragma unroll
+    for (int j = 0; j < m; ++j) {
+        const F2 t = v_add(v[2 * (j > 0 ? j - 1 : 0) + 1], v[2 * j + 1]);
+        v[2 * j] = f2_make(CVX_FMA(CVX_LB, f2_lo(t), a[2 * j]), CVX_FMA(CVX_LB, f2_hi(t), b[2 * j]));
+    }
+#pragma unroll
+    for (int j = 0; j < m; ++j) v[2 * j + 1] = v_fmac(CVX_LG, v_add(v[2 * j], v[2 * (j + 1 < m ? j + 1 : m - 1)]), v[2 * j + 1]);
+#pragma unroll
+    for (int j = 0; j < m; ++j) v[2 * j] = v_fmac(CVX_LD, v_add(v[2 * (j > 0 ? j - 1 : 0) + 1], v[2 * j + 1]), v[2 * j]);
+    if constexpr (N > 2) fwd_lift_levels<N, 2>(v);
+    lift_unpack_scale_fwd<N, 0>(v, oa, ob);
+}
+// a, b: interleaved (lifting) positions in; oa, ob: natural order out
+template <int N>
+CVX_HD void inv_lift_pair(const float* a, const float* b, float* oa, float* ob)
+{
+    constexpr int m = N / 2;
+    F2 v[N];
+    lift_pack_scale_inv<N, 0>(a, b, v);
+    if constexpr (N > 2) inv_lift_levels<N, 2>(v);
+#pragma unroll
+    for (int j = 0; j < m; ++j) v[2 * j] = v_fmac(-CVX_LD, v_add(v[2 * (j > 0 ? j - 1 : 0) + 1], v[2 * j + 1]), v[2 * j]);
+#pragma unroll
+    for (int j = 0; j < m; ++j) v[2 * j + 1] = v_fmac(-CVX_LG, v_add(v[2 * j], v[2 * (j + 1 < m ? j + 1 : m - 1)]), v[2 * j + 1]);
+#pragma unroll
+    for (int j = 0; j < m; ++j) {
+        const F2 t = v_add(v[2 * (j > 0 ? j - 1 : 0) + 1], v[2 * j + 1]);
+        oa[2 * j] = CVX_FMA(-CVX_LB, f2_lo(t), f2_lo(v[2 * j]));
+        ob[2 * j] = CVX_FMA(-CVX_LB, f2_hi(t), f2_hi(v[2 * j]));
+    }
+#pragma unroll
+    for (int j = 0; j < m; ++j) {
+        const int jn = j + 1 < m ? j + 1 : m - 1;
+        oa[2 * j + 1] = CVX_FMA(-CVX_LA, CVX_ADD(oa[2 * j], oa[2 * jn]), f2_lo(v[2 * j + 1]));
+        ob[2 * j + 1] = CVX_FMA(-CVX_LA, CVX_ADD(ob[2 * j], ob[2 * jn]), f2_hi(v[2 * j + 1]));
+    }
+}
+
 // interleaved position p  <->  sub-band index (low first, recursively; DC at 0)
 CVX_HD constexpr int lift_pos_to_idx(int p, int N)
 {

@@ -3,19 +3,25 @@
 Blocks are independent (zero padding + in-block mirror extension, Block_Copy.cpp:92-115,
 Wavelet_Transform_Slow.cpp:59-67), so any partition of whole blocks is valid.  Rank r of G owns the
 block rows [r*nbz//G, (r+1)*nbz//G): a contiguous iBlk range and a contiguous z-slab of the volume.
-The only couplings of the reference's Compress are two scalars:
+The reference parallelises ONE volume over its workers (CvxCompress.cpp:318, :528); the only couplings are two scalars:
 
-  * the global RMS (CvxCompress.cpp:73-117, :249)       -> all-gather of one fp64 sum of squares per rank,
-                                                           added in rank order on every rank
+  * the global RMS (CvxCompress.cpp:73-117, :249)       -> all-gather of the per-BLOCK-ROW fp64 sums of squares,
+                                                           added in row order on every rank: glob_mulfac, hence
+                                                           the whole stream, is identical for every G
   * the payload offsets (CvxCompress.cpp:365-390, :302) -> all-gather of one int64 payload size per rank,
                                                            exclusive prefix = the rank's base offset
 
 Decompress needs no collective.  No data-path collective exists; `assemble()` (optional) gathers the
 shards into one contiguous reference-format stream.
 
-The compute is behind a small backend interface.  The product backend is `CudaBackend` (ctypes ->
-cvxgpu_*_device, include/cvx_gpu.h); tests/ plug in a CPU checker backend to exercise this host logic
-under gloo without a GPU.  Nothing here imports oracle/.
+Two drivers of the same protocol:
+  * the product path (CUDA slabs, no `backend=`): `NcclShard`, a ctypes binding of the library's own C entry points
+    cvxgpu_compress_sharded / cvxgpu_decompress_sharded (csrc/cvx_shard.cpp: kernels + two ncclAllGather on the
+    caller's stream, no host synchronisation, CUDA-graph capturable).  torch.distributed only ships the 128-byte
+    NCCL unique id once;
+  * the host-logic path (`backend=` given): the same steps over torch.distributed collectives with the compute behind a
+    small backend interface -- tests/ plug in a CPU checker backend to exercise geometry, ordering and assembly under
+    gloo without a GPU.  Nothing here imports oracle/.
 """
 import ctypes as C
 
@@ -67,6 +73,14 @@ class CudaBackend:
             self._lib.check(self.L.cvxgpu_sumsq_device(None, slab.data_ptr(), slab.numel(), out.data_ptr(), self._st()))
         return out
 
+    def sumsq_rows(self, slab, g):
+        """fp64 sum of squares of every block row of the slab (cvxgpu_sumsq_rows_device): tensor[b1 - b0]."""
+        n = g.b1 - g.b0
+        out = torch.zeros(max(n, 1), dtype=torch.float64, device=slab.device)
+        if slab.numel():
+            self._lib.check(self.L.cvxgpu_sumsq_rows_device(None, slab.data_ptr(), g.nx * g.ny, g.bz, g.nz_slab, out.data_ptr(), self._st()))
+        return out[:n]
+
     def header(self, g, scale, local, sumsq_total):
         h = torch.zeros(32, dtype=torch.uint8, device=sumsq_total.device)
         self._lib.check(self.L.cvxgpu_write_header_device(h.data_ptr(), g.nx, g.ny, g.nz, g.bx, g.by, g.bz, float(scale),
@@ -105,7 +119,8 @@ class ShardedStream:
         """(glob_mulfac, payload bytes of this rank) as host values; read once (synchronises) and cached so that
         repeated decodes of the same stream stay asynchronous."""
         if getattr(self, "_meta", None) is None:
-            self._meta = (float(self.header[24:28].view(torch.float32).item()), int(self.nbytes.item()))
+            b = self.bases.cpu()
+            self._meta = (float(self.header[24:28].view(torch.float32).item()), int(b[self.geom.rank + 1] - b[self.geom.rank]))
         return self._meta
 
     def check(self):
@@ -128,30 +143,125 @@ def _all_gather_scalar(x, world, group):
     return out
 
 
-def compress_slab(slab, nx, ny, nz, bx, by, bz, scale, use_local_rms=False, payload=None, backend=None, group=None):
+class NcclShard:
+    """The product multi-GPU driver: this rank's cvxgpu_shard (NCCL communicator created inside the library from a unique
+    id that rank 0 draws and torch.distributed ships once), and one C call per direction."""
+
+    _cache = {}
+
+    def __init__(self, group=None):
+        from . import _lib
+        self._lib = _lib
+        self.L = _lib.lib()
+        self.rank, self.world = _world(group)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if self.world > 1:
+            if self.rank == 0:
+                buf = (C.c_ubyte * 128)()
+                _lib.check(self.L.cvxgpu_shard_unique_id(buf))
+                ident = torch.frombuffer(bytearray(buf), dtype=torch.uint8).clone()
+            on_gpu = dist.get_backend(group) == "nccl"
+            t = ident.to(self.device) if on_gpu else ident
+            dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            ident = t.cpu()
+        self.handle = C.c_void_p()
+        idbuf = (C.c_ubyte * 128).from_buffer_copy(bytes(ident.numpy().tobytes()))
+        with torch.cuda.device(self.device):
+            _lib.check(self.L.cvxgpu_shard_create(C.byref(self.handle), idbuf if self.world > 1 else None, None, self.rank, self.world))
+
+    @classmethod
+    def get(cls, group=None):
+        key = (id(group), torch.cuda.current_device())
+        if key not in cls._cache:
+            cls._cache[key] = cls(group)
+        return cls._cache[key]
+
+    def close(self):
+        if self.handle:
+            self.L.cvxgpu_shard_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    @staticmethod
+    def _st():
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def compress(self, slab, g, scale, local, payload=None, out=None):
+        dev = slab.device
+        n = g.nblk_slab
+        if out is None:
+            header = torch.zeros(32, dtype=torch.uint8, device=dev)
+            offs = torch.zeros(max(n, 1), dtype=torch.int64, device=dev)
+            bmf = torch.zeros(max(n, 1), dtype=torch.float32, device=dev) if local else None
+            bases = torch.zeros(self.world + 1, dtype=torch.int64, device=dev)
+            status = torch.zeros(1, dtype=torch.int32, device=dev)
+        else:                                   # reuse a previous ShardedStream's buffers (steady-state loops, graph capture)
+            header, offs, bmf, bases, status = out.header, out._offs_buf, out._bmf_buf, out.bases, out.status
+            payload = out.payload if payload is None else payload
+        if payload is None:
+            payload = torch.empty(default_payload_capacity(g, local), dtype=torch.uint8, device=dev)
+        self._lib.check(self.L.cvxgpu_compress_sharded(
+            self.handle, slab.data_ptr() if n else None, g.nx, g.ny, g.nz, g.bx, g.by, g.bz, float(scale), int(local),
+            header.data_ptr(), offs.data_ptr(), bmf.data_ptr() if local else None, payload.data_ptr(), payload.numel(),
+            bases.data_ptr(), status.data_ptr(), self._st()))
+        ss = ShardedStream(g, local, header, offs[:n], bmf[:n] if local else None, payload, None, bases, status)
+        ss._offs_buf, ss._bmf_buf, ss.driver = offs, bmf, self
+        return ss
+
+    def decompress(self, ss, out):
+        g = ss.geom
+        if g.nblk_slab == 0:
+            return out
+        self._lib.check(self.L.cvxgpu_decompress_sharded(
+            self.handle, out.data_ptr(), g.nx, g.ny, g.nz, g.bx, g.by, g.bz, int(ss.local), ss.header.data_ptr(),
+            ss.offs.data_ptr(), ss.bmf.data_ptr() if ss.local else None, ss.payload.data_ptr(), ss.bases.data_ptr(), self._st()))
+        return out
+
+
+def default_payload_capacity(g, local):
+    """Bytes reserved for a rank's payload when the caller gives no buffer: the worst case (every block of the slab raw,
+    cvxgpu_max_compressed_bytes minus header and tables) so that no data set can overflow it."""
+    return 4 * g.block_cells * max(g.nblk_slab, 1) + 64
+
+
+def compress_slab(slab, nx, ny, nz, bx, by, bz, scale, use_local_rms=False, payload=None, backend=None, group=None, out=None):
     """Compress this rank's z-slab (tensor [nz_slab, ny, nx]) of the global nx*ny*nz volume.
-    Everything is enqueued on the current stream; no host synchronisation.  Returns a ShardedStream."""
+    Everything is enqueued on the current stream; no host synchronisation.  Returns a ShardedStream.
+    `payload`: this rank's payload buffer (uint8); when omitted the worst case is allocated.  Call .check() (or
+    assemble(), which does) before trusting a stream written into a smaller buffer."""
     rank, world = _world(group)
     g = Geometry(nx, ny, nz, bx, by, bz, rank, world)
     assert tuple(slab.shape) == (g.nz_slab, ny, nx), "rank %d expects a slab of %d planes" % (rank, g.nz_slab)
-    be = backend or CudaBackend()
-    dev = slab.device
     local = bool(use_local_rms)
-    # (1) global RMS: per-rank sum of squares, all-gather, fixed (rank) order sum -> identical on every rank
+    if backend is None:
+        return NcclShard.get(group).compress(slab, g, scale, local, payload=payload, out=out)
+    be = backend
+    dev = slab.device
+    # (1) global RMS: per-block-row sums of squares, all-gather (padded to the largest rank), added in ROW order
     if local:
         sumsq_total = torch.zeros(1, dtype=torch.float64, device=dev)
     else:
-        parts = _all_gather_scalar(be.sumsq(slab), world, group)
-        sumsq_total = parts[0:1].clone()
-        for r in range(1, world):
-            sumsq_total += parts[r:r + 1]
+        counts = [slab_range(g.nbz, r, world)[1] - slab_range(g.nbz, r, world)[0] for r in range(world)]
+        seg = max(max(counts), 1)
+        mine = torch.zeros(seg, dtype=torch.float64, device=dev)
+        rows = be.sumsq_rows(slab, g)
+        mine[:rows.numel()] = rows
+        if world > 1:
+            allrows = torch.empty(world * seg, dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(allrows, mine, group=group)
+        else:
+            allrows = mine
+        sumsq_total = torch.zeros(1, dtype=torch.float64, device=dev)
+        for r in range(world):
+            for i in range(counts[r]):
+                sumsq_total += allrows[r * seg + i]
     header = be.header(g, scale, local, sumsq_total)
     # (2) this rank's blocks -> local table slice + local payload
     n = g.nblk_slab
     offs = torch.zeros(max(n, 1), dtype=torch.int64, device=dev)
     bmf = torch.zeros(max(n, 1), dtype=torch.float32, device=dev) if local else None
     if payload is None:
-        payload = torch.empty(max(slab.numel(), 4096) + 64, dtype=torch.uint8, device=dev)     # 1/4 of the raw slab
+        payload = torch.empty(default_payload_capacity(g, local), dtype=torch.uint8, device=dev)
     nbytes = torch.zeros(1, dtype=torch.int64, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     if n:
@@ -163,40 +273,59 @@ def compress_slab(slab, nx, ny, nz, bx, by, bz, scale, use_local_rms=False, payl
     bases[1:] = torch.cumsum(sizes, 0)
     if n:
         offs[:n] += bases[rank]
-    return ShardedStream(g, local, header, offs[:n], bmf[:n] if local else None, payload, nbytes, bases, status)
+    ss = ShardedStream(g, local, header, offs[:n], bmf[:n] if local else None, payload, nbytes, bases, status)
+    ss.driver = None
+    return ss
 
 
 def decompress_slab(ss, out=None, backend=None):
-    """Decode this rank's blocks of a ShardedStream into its z-slab [nz_slab, ny, nx].  No collective."""
+    """Decode this rank's blocks of a ShardedStream into its z-slab [nz_slab, ny, nx].  No collective; on the product
+    path no host synchronisation either (glob_mulfac, the payload extent and the offset bias are read on the device)."""
     g = ss.geom
-    be = backend or CudaBackend()
     dev = ss.payload.device
     if out is None:
         out = torch.empty((g.nz_slab, g.ny, g.nx), dtype=torch.float32, device=dev)
     if g.nblk_slab == 0:
         return out
-    glob_mulfac, nbytes = ss.host_meta()                     # the C ABI takes both by value
+    if backend is None and getattr(ss, "driver", None) is not None:
+        return ss.driver.decompress(ss, out)
+    ss.check()
+    be = backend or CudaBackend()
+    glob_mulfac, nbytes = ss.host_meta()                     # the piecewise C ABI takes both by value
     offs_local = ss.offs - ss.bases[g.rank]
     be.decode_blocks(out, g, glob_mulfac, ss.local, offs_local, ss.bmf, ss.payload, nbytes)
     return out
 
 
-def decompress_slab_from_stream(stream, length, rank=None, world=None, out=None, backend=None, group=None):
+def decompress_slab_from_stream(stream, length, rank=None, world=None, out=None, backend=None, group=None, header=None):
     """Decode this rank's iBlk range from a FULL reference-format stream (any block order, e.g. one written by
-    the reference with several threads, CvxCompress.cpp:365-390) held by every rank.  No collective."""
+    the reference with several threads, CvxCompress.cpp:365-390) held by every rank.  No collective.
+    `header`: (nx, ny, nz, bx, by, bz, use_local_rms) when the caller knows it -- the call then does not read the
+    stream's first 32 bytes back (no host synchronisation; glob_mulfac is read on the device)."""
     r, w = _world(group)
     rank = r if rank is None else rank
     world = w if world is None else world
-    be = backend or CudaBackend()
-    hdr = stream[:32].cpu()
-    nx, ny, nz, bx, by, bz = (int(v) for v in hdr[:24].view(torch.int32))
-    glob_mulfac = float(hdr[24:28].view(torch.float32)[0])
-    local = bool(int(hdr[28:32].view(torch.int32)[0]) & 1)
+    if header is None:
+        hdr = stream[:32].cpu()
+        nx, ny, nz, bx, by, bz = (int(v) for v in hdr[:24].view(torch.int32))
+        local = bool(int(hdr[28:32].view(torch.int32)[0]) & 1)
+    else:
+        nx, ny, nz, bx, by, bz, local = header
+        local = bool(local)
     g = Geometry(nx, ny, nz, bx, by, bz, rank, world)
     if out is None:
         out = torch.empty((g.nz_slab, ny, nx), dtype=torch.float32, device=stream.device)
     if g.nblk_slab == 0:
         return out, g
+    if backend is None:
+        from . import _lib
+        with torch.cuda.device(stream.device):
+            _lib.check(_lib.lib().cvxgpu_decompress_slab_device(
+                None, out.data_ptr(), nx, ny, nz, bx, by, bz, int(local), rank, world, stream.data_ptr(), int(length),
+                C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return out, g
+    be = backend
+    glob_mulfac = float(stream[24:28].cpu().view(torch.float32)[0])
     tb = g.table_bytes(local)
     offs = stream[32:32 + 8 * g.nblk].view(torch.int64)[g.blk_first:g.blk_first + g.nblk_slab]
     bmf = None
@@ -213,6 +342,7 @@ def assemble(ss, group=None):
     g = ss.geom
     rank, world = _world(group)
     dev = ss.payload.device
+    ss.check()                      # a payload buffer that was too small leaves a truncated shard: refuse to assemble it
     bases = ss.bases.cpu()
     total = int(bases[-1])
     tb = g.table_bytes(ss.local)

@@ -56,11 +56,17 @@ int  cvxgpu_device_count(void);
 int  cvxgpu_set_transform(int mode);
 int  cvxgpu_get_transform(void);
 
-/* scratch owned by the caller: look-back status words, partial sums, staging.  One workspace
- * must not be used by two host threads at once.  NULL may be passed to every call below, in
- * which case a per-host-thread default workspace on the current device is used. */
+/* scratch owned by the caller: look-back status words, ticket, partial sums, staging -- the state of
+ * ONE call in flight.  A workspace must not be used by two host threads at once, nor by two calls
+ * that can overlap on the GPU (calls enqueued on different CUDA streams).  NULL may be passed to
+ * every call below: the library then uses a default workspace of the calling host thread, one per
+ * (current device, cuda_stream) pair, so that calls a thread enqueues on different streams never
+ * share state; calls on one stream are ordered by the stream.  A default workspace is created by
+ * the first call that needs it (device allocations: make that call outside a CUDA-graph capture);
+ * cvxgpu_workspace_release_thread_default() synchronises and frees the calling thread's. */
 int  cvxgpu_workspace_create(cvxgpu_workspace** ws);
 int  cvxgpu_workspace_destroy(cvxgpu_workspace* ws);
+int  cvxgpu_workspace_release_thread_default(void);
 
 int  cvxgpu_is_valid_block_size(int bx, int by, int bz);
 long cvxgpu_num_blocks(int nx, int ny, int nz, int bx, int by, int bz);
@@ -148,6 +154,15 @@ int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void* stream_in,
  * Decompress needs no collective: every rank decodes its own iBlk range from the full stream. */
 int cvxgpu_sumsq_device(cvxgpu_workspace* ws, const float* d_vol, long ncells, double* d_sumsq, void* cuda_stream);
 
+/* The same reduction per BLOCK ROW (the planes [i*bz, (i+1)*bz) of a volume or of a z-slab that starts
+ * on a block-row boundary): d_rowsums[(nz + bz - 1) / bz].  Every row's sum is formed in an order that
+ * depends on the row alone, and cvxgpu_sum_rows_device adds rows one after the other, so the global RMS
+ * -- hence glob_mulfac and every byte of the stream -- is the same for any number of slabs
+ * (Compute_Global_RMS, CvxCompress.cpp:73-117).  cvxgpu_compress_device uses these two. */
+int cvxgpu_sumsq_rows_device(cvxgpu_workspace* ws, const float* d_vol, long plane_cells, int bz, int nz,
+                             double* d_rowsums, void* cuda_stream);
+int cvxgpu_sum_rows_device(const double* d_rowsums, int nrows, double* d_total, void* cuda_stream);
+
 /* Encode the blocks of a volume (or slab) of nx*ny*nz_slab cells.  d_sumsq_total / ncells_total
  * define the global RMS (ignored when use_local_rms).  d_offs receives nblk entries (payload
  * offsets relative to d_payload, bit 63 = raw), d_blkmulfac nblk floats when use_local_rms (else
@@ -171,6 +186,48 @@ int cvxgpu_decode_blocks_device(cvxgpu_workspace* ws, float* d_vol_slab, int nx,
                                 int bx, int by, int bz, float glob_mulfac, int use_local_rms,
                                 const unsigned long long* d_offs, const float* d_blkmulfac,
                                 const void* d_payload, long payload_bytes, void* cuda_stream);
+
+/* ---- z-slab sharding behind one call per direction (one process or host thread per GPU) -----------
+ * The reference parallelises ONE volume over its workers (CvxCompress.cpp:318 and :528, OpenMP over the
+ * blocks); here the workers are GPUs.  Rank r of `world` owns the block rows [r*nbz/world, (r+1)*nbz/world)
+ * (cvxgpu_shard_range): a contiguous z-slab of the volume and a contiguous iBlk range of the tables.
+ * A cvxgpu_shard holds the rank's NCCL communicator, workspace and protocol scratch.  NCCL is bound at run
+ * time (symbols already in the process, else libnccl.so.2 / $CVX_GPU_NCCL_LIB): pass either the 128-byte
+ * ncclUniqueId all ranks share (cvxgpu_shard_unique_id on rank 0, shipped by any means; the shard then
+ * calls ncclCommInitRank on the current device and owns the communicator) or an existing `ncclComm_t`
+ * as `nccl_comm`.  world == 1 needs neither.
+ *
+ * cvxgpu_compress_sharded enqueues on cuda_stream, without host synchronisation (CUDA-graph capturable
+ * after one eager call):  block-row sums of squares of the slab -> ncclAllGather -> fixed-order total ->
+ * header + glob_mulfac -> encode the slab's blocks -> ncclAllGather of the payload sizes -> exclusive
+ * prefix, offsets made global.  Outputs, all DEVICE memory of this rank:
+ *   d_header   32 bytes, identical on every rank (CvxCompress.cpp:284-300)
+ *   d_offs     this rank's slice of the offset table, nblk_slab entries, offsets relative to the GLOBAL
+ *              payload start (bit 63 = raw);  d_blkmulfac  its slice of the multiplier table (local RMS)
+ *   d_payload  this rank's payload bytes; they start at byte d_bases[rank] of the global payload
+ *   d_bases    world + 1 int64: exclusive prefix of the ranks' payload sizes, d_bases[world] = total, so
+ *              compressed_length = 32 + 8*nnn [+ 4*nnn] + d_bases[world] + 7
+ *   d_status   0 or CVXGPU_ERR_CAPACITY (payload_capacity too small for this slab)
+ * The concatenation header | tables in rank order | payloads in rank order is byte for byte the stream
+ * cvxgpu_compress_device writes for the whole volume, for every `world`.
+ * cvxgpu_decompress_sharded decodes the rank's slice back into its slab (no collective; d_payload must be
+ * 16-byte aligned).  cvxgpu_decompress_slab_device decodes the rank's iBlk range out of a FULL stream every
+ * rank holds (any block order, e.g. one written by the reference with several threads). */
+typedef struct cvxgpu_shard cvxgpu_shard;
+int cvxgpu_shard_range(int nz, int bz, int rank, int world, int* z0, int* nz_slab, int* block_row0, int* n_block_rows);
+int cvxgpu_shard_unique_id(void* id128);
+int cvxgpu_shard_create(cvxgpu_shard** sh, const void* id128, void* nccl_comm, int rank, int world);
+int cvxgpu_shard_destroy(cvxgpu_shard* sh);
+int cvxgpu_compress_sharded(cvxgpu_shard* sh, const float* d_slab, int nx, int ny, int nz, int bx, int by, int bz,
+                            float scale, int use_local_rms, void* d_header, unsigned long long* d_offs,
+                            float* d_blkmulfac, void* d_payload, long payload_capacity, long* d_bases,
+                            int* d_status, void* cuda_stream);
+int cvxgpu_decompress_sharded(cvxgpu_shard* sh, float* d_slab, int nx, int ny, int nz, int bx, int by, int bz,
+                              int use_local_rms, const void* d_header, const unsigned long long* d_offs,
+                              const float* d_blkmulfac, const void* d_payload, const long* d_bases, void* cuda_stream);
+int cvxgpu_decompress_slab_device(cvxgpu_workspace* ws, float* d_slab, int nx, int ny, int nz, int bx, int by, int bz,
+                                  int use_local_rms, int rank, int world, const void* d_stream, long length,
+                                  void* cuda_stream);
 
 /* ---- wavelet only: nblocks dense blocks (x fastest), in place (config 2 sweep) ------------- */
 int cvxgpu_wavelet_blocks_device(cvxgpu_workspace* ws, float* d_blocks, long nblocks, int bx, int by, int bz,

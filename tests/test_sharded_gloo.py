@@ -25,6 +25,11 @@ class OracleBackend:
         v = slab.numpy().astype(np.float64)
         return torch.tensor([float(np.sum(v * v))], dtype=torch.float64)
 
+    def sumsq_rows(self, slab, g):
+        v = slab.numpy().astype(np.float64)
+        rows = [float(np.sum(v[i * g.bz:(i + 1) * g.bz] ** 2)) for i in range(g.b1 - g.b0)]
+        return torch.tensor(rows, dtype=torch.float64)
+
     @staticmethod
     def _glob_mulfac(g, scale, local, sumsq_total):
         rms = np.float32(1.0) if local else np.float32(np.sqrt(float(sumsq_total.item()) / g.ncells))

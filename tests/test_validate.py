@@ -205,3 +205,19 @@ def test_threaded_walk_equals_serial_walk(monkeypatch):
         monkeypatch.setenv("CVX_GPU_VALIDATE_THREADS", threads)
         with pytest.raises(_lib.CvxError, match="block 1234:"):
             api.validate_stream(bad)
+
+
+def test_overflowing_header_is_refused_not_fatal():
+    """A crafted header whose block count overflows 64 bits (16777216 x 16777216 x 8388608 cells in 8^3 blocks: nblk = 2^62,
+    8 * nblk wraps to 0) must come back as CVXGPU_ERR_STREAM -- no allocation, no exception across the C ABI."""
+    buf = np.zeros(96, np.uint8)
+    hdr = np.array([16777216, 16777216, 8388608, 8, 8, 8], np.int32)
+    buf[:24] = hdr.view(np.uint8)
+    buf[24:28] = np.frombuffer(np.float32(1.0).tobytes(), np.uint8)
+    with pytest.raises(_lib.CvxError, match="cannot hold"):
+        api.validate_stream(buf)
+    # dimensions next to INT_MAX: nx + bx - 1 overflows a 32-bit int
+    hdr = np.array([2147483647, 2147483647, 2147483647, 256, 256, 256], np.int32)
+    buf[:24] = hdr.view(np.uint8)
+    with pytest.raises(_lib.CvxError, match="cannot hold"):
+        api.validate_stream(buf)
