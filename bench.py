@@ -318,7 +318,7 @@ def numa_bind(local_rank):
         path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
         node = int(open(path).read().strip())
         if node < 0:
-            return None
+            return {"numa_node": node, "note": "the box exposes no NUMA topology for this GPU; nothing bound"}
         cpus = []
         for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
             lo, _, hi = part.partition("-")
@@ -583,7 +583,6 @@ def run_ours(args):
                                "decompress_frac": dbytes / (td_ms * 1e-3) / 1e9 / peak,
                                "compress_frac_of_8TBs": cbytes / (tc_ms * 1e-3) / 1e9 / 8000.0,
                                "decompress_frac_of_8TBs": dbytes / (td_ms * 1e-3) / 1e9 / 8000.0}}
-    del pay_t, offs_t
     err_end = rt.error()                            # out_slab now holds the last timed k_decode launch's output
     check_quality(err_end, "after the timed region")
     err = max(err, err_end)
@@ -732,6 +731,275 @@ def e2e_legs(args, rt, L, barrier, K):
     return res[0], res[1]
 
 
+# ---- BASELINE config 5: decompress-only, stream written by the reference on the host cores ------------------
+def run_config5(args):
+    """1280^3 G2 volume.  Rank 0 builds it on the host and lets the UNMODIFIED reference write the stream with all host
+    cores (permuted block order, CvxCompress.cpp:365-390); every rank receives the whole stream and decodes its own iBlk
+    range into its z-slab (cvxgpu_decompress_slab_device, no collective).  Checked against the reference's own decode of
+    the same stream; the reverse direction (GPU stream -> reference decoder) is checked too."""
+    import numpy as np
+    import torch
+    rank, world, local_rank, dev, numa = init_dist()
+    import torch.distributed as dist
+    from cvxcompress_b200 import _lib, api, sharded, synth
+    L = _lib.lib()
+    api.set_transform(args.transform)
+    K, W = args.steps, args.warmup
+    g = sharded.Geometry(NX, NY, NZ, BX, BY, BZ, rank, world)
+    cells_total = NX * NY * NZ
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    cpu_info = None
+    meta = torch.zeros(2, dtype=torch.int64, device=dev)
+    host_vol = ref_out = None
+    if rank == 0:
+        host_vol = np.empty((NZ, NY, NX), np.float32)
+        for z0 in range(0, NZ, 64):
+            n = min(64, NZ - z0)
+            host_vol[z0:z0 + n] = synth.g2_torch(NX, NY, n, dev, z0=z0, nz_total=NZ).cpu().numpy()
+        cpu = CpuPath()
+        cpu.prepare(host_vol)
+        t_c = cpu.compress()
+        t_d = cpu.decompress()
+        ref_out = cpu.out.reshape(NZ, NY, NX)
+        length = int(cpu.length.value)
+        e_ref, snr_ref = quality_np(host_vol, ref_out)
+        cpu_info = {"value": cells_total / t_d / 1e6, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
+                    "compress_mcells_s": cells_total / t_c / 1e6, "decompress_mcells_s": cells_total / t_d / 1e6,
+                    "sample": "the whole %dx%dx%d volume, one Compress (%.2f s) and one Decompress (%.2f s), threads=%d" % (
+                        NX, NY, NZ, t_c, t_d, cpu.cores),
+                    "compressed_length": length, "ratio": 4.0 * cells_total / length, "snr_db": snr_ref}
+        meta[0] = length
+        stream = torch.zeros((length + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+        stream[:length] = torch.from_numpy(np.ascontiguousarray(cpu.stream[:length])).to(dev)
+    if world > 1:
+        dist.broadcast(meta, src=0)
+    length = int(meta[0].item())
+    if rank != 0:
+        stream = torch.zeros((length + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+    if world > 1:
+        dist.broadcast(stream, src=0)
+    out_slab = torch.empty((g.nz_slab, NY, NX), dtype=torch.float32, device=dev)
+    hdr = (NX, NY, NZ, BX, BY, BZ, LOCAL)
+
+    def do_decode():
+        sharded.decompress_slab_from_stream(stream, length, rank=rank, world=world, out=out_slab, header=hdr)
+
+    do_decode(); torch.cuda.synchronize()
+    for _ in range(W):
+        do_decode()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    sampler = ClockSampler(local_rank)
+    barrier(); sampler.start()
+    ev[0].record()
+    for k in range(K):
+        do_decode(); ev[k + 1].record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop(); barrier()
+    tm = torch.tensor([ev[0].elapsed_time(ev[K]) / K], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms = float(tm.item())
+    peak, peak_src = measured_peak_gbs()
+    # ---- parity: every rank's slab against the reference's decode of the same stream ----
+    ref_slab = torch.empty_like(out_slab)
+    if world > 1:
+        if rank == 0:
+            for r in range(world - 1, -1, -1):
+                gr = sharded.Geometry(NX, NY, NZ, BX, BY, BZ, r, world)
+                t = torch.from_numpy(ref_out[gr.z0:gr.z1]).to(dev)
+                if r == 0:
+                    ref_slab.copy_(t)
+                else:
+                    dist.send(t, dst=r)
+        else:
+            dist.recv(ref_slab, src=0)
+    else:
+        ref_slab.copy_(torch.from_numpy(ref_out))
+    st = torch.stack([(out_slab - ref_slab).abs().max().double(), ref_slab.abs().max().double(),
+                      (out_slab != ref_slab).sum().double()])
+    if world > 1:
+        mx = st[:2].clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = st[2:].clone(); dist.all_reduce(sm)
+        st = torch.cat([mx, sm])
+    maxdiff, maxref, ndiff = (float(v) for v in st.tolist())
+    tol = 1e-6 if args.transform == "exact" else 2e-5
+    if not (maxdiff <= tol * maxref):
+        sys.stderr.write("bench.py: INVALID RUN: GPU decode of the reference stream differs from the reference's decode by %g (max |v| %g)\n" % (maxdiff, maxref))
+        sys.exit(3)
+    # ---- reverse direction: a GPU-written stream through the reference decoder (rank 0, N == 1 only: it needs the volume on one GPU) ----
+    reverse = None
+    if world == 1:
+        vol_d = torch.from_numpy(host_vol).to(dev)
+        s2, ln2, _ = api.compress_device(vol_d, BX, BY, BZ, SCALE, LOCAL)
+        gpu_dec = api.decompress_device(s2, ln2, NX, NY, NZ)
+        h_s2 = s2[:ln2].cpu().numpy()
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_libs as ol
+        if ol.have_ref():
+            buf = ol.aligned_u8(ln2 + 64); buf[:ln2] = h_s2
+            out2 = np.zeros(cells_total, np.float32)
+            ol.ref().cvx_decompress_inplace_th(out2, NX, NY, NZ, buf, host_cores(), ln2)
+            d2 = float((gpu_dec - torch.from_numpy(out2.reshape(NZ, NY, NX)).to(dev)).abs().max().item())
+            reverse = {"gpu_stream_bytes": int(ln2), "max_abs_diff_reference_decode_vs_gpu_decode": d2, "max_abs_value": maxref,
+                       "within": tol * maxref, "ok": d2 <= tol * maxref,
+                       "length_rel_diff_vs_reference_stream": (length - ln2) / float(length)}
+            if not reverse["ok"]:
+                sys.stderr.write("bench.py: INVALID RUN: reference decode of the GPU stream differs from the GPU decode by %g\n" % d2)
+                sys.exit(3)
+        del vol_d, s2, gpu_dec
+    # ---- e2e: host stream in, host slab out ----
+    e2e = None
+    if not args.no_e2e:
+        h_stream = torch.empty(length + 64, dtype=torch.uint8, pin_memory=True)
+        h_stream[:length].copy_(stream[:length])
+        h_out = torch.empty(out_slab.shape, dtype=torch.float32, pin_memory=True)
+        torch.cuda.synchronize()
+        if world == 1:
+            def step():
+                L.cvx_decompress_inplace_th(h_out.data_ptr(), NX, NY, NZ, h_stream.data_ptr(), 1, length)
+        else:
+            def step():
+                stream[:length].copy_(h_stream[:length], non_blocking=True)
+                do_decode()
+                h_out.copy_(out_slab, non_blocking=True)
+                torch.cuda.synchronize()
+        step(); barrier()
+        ke = max(2, min(K, 4))
+        t0 = time.perf_counter()
+        for _ in range(ke):
+            step()
+        torch.cuda.synchronize()
+        tt = torch.tensor([(time.perf_counter() - t0) / ke], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        te = float(tt.item())
+        e2e = {"value": cells_total / te / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(length), "d2h_bytes_per_step": int(4 * out_slab.numel()),
+               "ms_per_step": te * 1e3, "steps": ke, "host_memory": "pinned",
+               "api": "cvx_decompress_inplace_th (host pointers)" if world == 1 else "H2D stream + cvxgpu_decompress_slab_device + D2H slab, per rank"}
+    if rank == 0:
+        tb = 8 * g.nblk
+        abytes = 4 * out_slab.numel() + (length - 32 - tb) * (g.nblk_slab / float(g.nblk)) + 8 * g.nblk_slab
+        gbs = abytes / (ms * 1e-3) / 1e9
+        line = {"metric": metric_name(args, world), "value": cells_total / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload_config(args, world), "compressed_length": length, "ratio": 4.0 * cells_total / length,
+                "parity": {"max_abs_diff_vs_reference_decode": maxdiff, "max_abs_value": maxref, "cells_differing": ndiff,
+                           "tolerance": tol * maxref, "stream_block_order": "reference, %d threads (permuted)" % (cpu_info or {}).get("cores", 0),
+                           "reverse": reverse},
+                "roofline": {"bound": "hbm", "kernel": "k_decode32ws" if args.transform == "lifting" else "k_decode32", "achieved": gbs, "peak": peak,
+                             "unit": "GB/s", "frac": gbs / peak, "traffic": None, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": abytes, "ms_per_launch": ms},
+                "cpu_baseline": cpu_info, "e2e": e2e, "clocks": clocks, "gpu_launches": K,
+                "gpu_launches_detail": "per step and rank: one decode kernel over the rank's iBlk range", "numa": numa}
+        emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ---- BASELINE config 2: wavelet forward + inverse sweep over cubes 8^3 .. 256^3 ------------------------------
+SWEEP = (8, 16, 32, 64, 128, 256)
+
+
+def run_wavelet(args):
+    """CvxCompress_Test's throughput sweep (CvxCompress.cpp:803-891): forward then inverse 9/7 transform of dense cubes.
+    The reference re-transforms ONE cache-resident block per thread (2^30 cells' worth of repetitions); here 2^30 cells of
+    DISTINCT blocks (4 GiB) stream through HBM: 16*N algorithmic bytes per forward + inverse pair."""
+    import torch
+    rank, world, local_rank, dev, numa = init_dist()
+    from cvxcompress_b200 import api, synth
+    api.set_transform(args.transform)
+    K, W = args.steps, args.warmup
+    ncell = 1 << 30
+    if args.nz:
+        ncell = max(1 << 24, (args.nz * 1056 * 1248) // (1 << 24) * (1 << 24))
+    peak, peak_src = measured_peak_gbs()
+    idx = torch.arange(ncell, dtype=torch.int64, device=dev)
+    src = ((synth._hash32_torch(idx) >> 8).to(torch.float32) / float(1 << 24)) * 2.0 - 1.0       # U(-1, 1), as Fill_Block's range
+    del idx
+    buf = torch.empty_like(src)
+    sweep = {}
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    for b in SWEEP:
+        nblocks = ncell // (b * b * b)
+        blocks = buf.view(nblocks, b, b, b)
+        buf.copy_(src)
+        api.wavelet_blocks_device(blocks, b, b, b, inverse=False)
+        api.wavelet_blocks_device(blocks, b, b, b, inverse=True)
+        torch.cuda.synchronize()
+        err = float((buf - src).abs().max().item())
+        tf = time_kernel(lambda: api.wavelet_blocks_device(blocks, b, b, b, inverse=False), max(2, min(K, 5)))
+        ti = time_kernel(lambda: api.wavelet_blocks_device(blocks, b, b, b, inverse=True), max(2, min(K, 5)))
+        gbs = 16.0 * ncell / ((tf + ti) * 1e-3) / 1e9
+        sweep["%d^3" % b] = {"forward_ms": tf, "inverse_ms": ti, "mcells_s": ncell / ((tf + ti) * 1e-3) / 1e6,
+                             "achieved_gbs": gbs, "frac": gbs / peak, "max_roundtrip_error": err, "blocks": nblocks}
+    clocks = sampler.stop()
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        try:
+            cpu = wavelet_cpu_leg()
+        except Exception as e:
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(e)}
+    if rank == 0:
+        top = sweep["32^3"]
+        line = {"metric": "Wavelet forward+inverse MCells/s, cubes 8^3..256^3, %d cells of distinct blocks (value = 32^3)" % ncell,
+                "value": top["mcells_s"], "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W, "ms_per_step": top["forward_ms"] + top["inverse_ms"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "BASELINE config 2: CvxCompress_Test wavelet fwd+inv throughput sweep, block sizes 8^3..256^3, "
+                                       "G3 data U(-1,1), %d cells (%.1f GiB) of distinct dense blocks per size" % (ncell, ncell * 4 / 2 ** 30),
+                           "config": 2, "transform": args.transform, "cells": ncell,
+                           "l2": "inputs larger than L2 (4 GiB per pass vs 126 MB L2); no flush needed"},
+                "sweep": sweep,
+                "roofline": {"bound": "hbm", "kernel": "k_wavelet_fused (32^3)", "achieved": top["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                             "frac": top["frac"], "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": 8 * ncell,
+                             "ms_per_launch": 0.5 * (top["forward_ms"] + top["inverse_ms"])},
+                "cpu_baseline": cpu, "e2e": None, "clocks": clocks, "gpu_launches": 2 * len(SWEEP) * max(2, min(K, 5)), "numa": numa}
+        emit(line)
+
+
+def wavelet_cpu_leg(budget_s=3.0):
+    """The reference's Wavelet_Transform_Fast_{Forward,Inverse} (oracle/_ref) on one cube per size, one thread, repeated for
+    ~budget_s / size -- its own benchmark's cache-resident regime (CvxCompress.cpp:826-857)."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_libs as ol
+    if not ol.have_ref():
+        raise RuntimeError("oracle/_ref not built")
+    R = ol.ref()
+    from cvxcompress_b200 import synth
+    res = {}
+    for b in SWEEP:
+        n = b * b * b
+        blk = ol.aligned_f32(n)
+        blk[:] = synth.g3(n, lo=-1.0, hi=1.0)
+        work = ol.aligned_f32(max(n, 1 << 16))
+        reps, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < budget_s / len(SWEEP) or reps < 2:
+            R.fwd_fast(blk.ctypes.data, work.ctypes.data, b, b, b)
+            R.inv_fast(blk.ctypes.data, work.ctypes.data, b, b, b)
+            reps += 1
+        dt = time.perf_counter() - t0
+        res["%d^3" % b] = {"mcells_s": reps * n / dt / 1e6, "pairs": reps}
+    return {"value": res["32^3"]["mcells_s"], "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": "Wavelet_Transform_Fast_Forward + _Inverse of one cache-resident cube per size, 1 thread, ~%.1f s per size" % (budget_s / len(SWEEP)),
+            "sweep": res}
+
+
+def run_reference_wavelet(args):
+    info = wavelet_cpu_leg(budget_s=max(6.0, 2.0 * args.steps))
+    emit({"impl": "reference", "metric": "Wavelet forward+inverse MCells/s, cubes 8^3..256^3 (value = 32^3)", "value": info["value"], "unit": UNIT,
+          "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "strong",
+          "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+          "config": {"workload": "BASELINE config 2 on the host: " + info["sample"], "config": 2}, "cpu_baseline": info,
+          "e2e": {"value": info["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
+
+
 _RESULT_FD = None
 
 
@@ -757,6 +1025,7 @@ def emit(line):
 
 def main():
     args = parse_args()
+    select_config(args)
     _claim_stdout()
     if args.impl == "reference":
         run_reference(args)

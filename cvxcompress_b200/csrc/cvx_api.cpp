@@ -92,6 +92,7 @@ extern "C" int cvxgpu_workspace_create(cvxgpu_workspace** out)
     *out = nullptr;
     int dev = 0;
     CU(cudaGetDevice(&dev));
+    CvxRelaxCapture relax;               // a default workspace may be born under a stream capture (first call on the capture stream)
     cvxgpu_workspace* ws = new cvxgpu_workspace();
     ws->device = dev;
     cudaDeviceProp prop;
@@ -99,7 +100,7 @@ extern "C" int cvxgpu_workspace_create(cvxgpu_workspace** out)
     if (e != cudaSuccess) { delete ws; return fail(CVXGPU_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
     ws->sm_count = prop.multiProcessorCount;
     ws->n_partial = ws->sm_count * 8;
-    if ((e = cudaMalloc(&ws->d_scalars, 256)) != cudaSuccess || (e = cudaMemset(ws->d_scalars, 0, 256)) != cudaSuccess ||
+    if ((e = cudaMalloc(&ws->d_scalars, 256)) != cudaSuccess ||
         (e = cudaMalloc(&ws->d_partial, sizeof(double) * ws->n_partial)) != cudaSuccess ||
         (e = cudaMallocHost(&ws->h_pinned, 256)) != cudaSuccess) {
         cvxgpu_workspace_destroy(ws);
@@ -125,6 +126,8 @@ extern "C" int cvxgpu_workspace_destroy(cvxgpu_workspace* ws)
     if (ws->h_pinned) cudaFreeHost(ws->h_pinned);
     if (ws->d_stage_vol) cudaFree(ws->d_stage_vol);
     if (ws->d_stage_stream) cudaFree(ws->d_stage_stream);
+    if (ws->h_stage) cudaFreeHost(ws->h_stage);
+    if (ws->priv_stream) cudaStreamDestroy(ws->priv_stream);
     if (ws->d_rowpartial) cudaFree(ws->d_rowpartial);
     if (ws->d_rowsum) cudaFree(ws->d_rowsum);
     delete ws;
@@ -651,14 +654,12 @@ static int reserve(unsigned char** p, size_t* have, size_t want)
     return CVXGPU_OK;
 }
 
-// chunked copies keep pageable transfers pipelined inside the driver and bound pinned staging
-static int copy_chunked(void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st)
+// the host-pointer entry points run on a private non-blocking stream of the calling thread's workspace: the legacy
+// stream 0 would serialise against every other stream of the host application
+static int priv_stream(cvxgpu_workspace* ws, cudaStream_t* st)
 {
-    const size_t chunk = 256ull << 20;
-    for (size_t o = 0; o < bytes; o += chunk) {
-        size_t n = bytes - o < chunk ? bytes - o : chunk;
-        CU(cudaMemcpyAsync(static_cast<unsigned char*>(dst) + o, static_cast<const unsigned char*>(src) + o, n, kind, st));
-    }
+    if (!ws->priv_stream) CU(cudaStreamCreateWithFlags(&ws->priv_stream, cudaStreamNonBlocking));
+    *st = ws->priv_stream;
     return CVXGPU_OK;
 }
 
@@ -675,12 +676,14 @@ extern "C" int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx,
     const size_t vol_bytes = (size_t)nx * ny * nz * 4;
     const long max_bytes = cvxgpu_max_compressed_bytes(nx, ny, nz, bx, by, bz, local);
     const int vol_dev = pointer_on_device(vol), out_dev = pointer_on_device(stream_out);
-    cudaStream_t st = 0;
+    cudaStream_t st;
+    rc = priv_stream(ws, &st);
+    if (rc) return rc;
     const float* d_vol = vol;
     if (!vol_dev) {
         rc = reserve(&ws->d_stage_vol, &ws->stage_vol_bytes, vol_bytes);
         if (rc) return rc;
-        rc = copy_chunked(ws->d_stage_vol, vol, vol_bytes, cudaMemcpyHostToDevice, st);
+        rc = cvx_stage_upload(ws, ws->d_stage_vol, vol, vol_bytes, st);      // pinned: one DMA; pageable: threaded bounce buffers
         if (rc) return rc;
         d_vol = reinterpret_cast<const float*>(ws->d_stage_vol);
     }
@@ -701,10 +704,7 @@ extern "C" int cvxgpu_compress(const float* vol, int nx, int ny, int nz, int bx,
     }
     if (rc) return rc;
     // only [0, length - 7) is written: the final 7 slack bytes are never touched (CvxCompress.cpp:421)
-    rc = copy_chunked(stream_out, ws->d_stage_stream, (size_t)(*length - 7), cudaMemcpyDeviceToHost, st);
-    if (rc) return rc;
-    CU(cudaStreamSynchronize(st));
-    return CVXGPU_OK;
+    return cvx_stage_download(ws, stream_out, ws->d_stage_stream, (size_t)(*length - 7), st);
 }
 
 extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void* stream_in, long length)
@@ -714,8 +714,15 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
     if (rc) return rc;
     if (!vol || !stream_in) return fail(CVXGPU_ERR_ARG, "cvxgpu_decompress: null pointer");
     const int vol_dev = pointer_on_device(vol), in_dev = pointer_on_device(stream_in);
-    cudaStream_t st = 0;
-    if (in_dev && vol_dev) return cvxgpu_decompress_device(ws, vol, nx, ny, nz, stream_in, length, st);
+    cudaStream_t st;
+    rc = priv_stream(ws, &st);
+    if (rc) return rc;
+    if (in_dev && vol_dev) {
+        rc = cvxgpu_decompress_device(ws, vol, nx, ny, nz, stream_in, length, st);
+        if (rc) return rc;
+        CU(cudaStreamSynchronize(st));
+        return CVXGPU_OK;
+    }
     int32_t h[8];
     if (in_dev) {
         if (reinterpret_cast<uintptr_t>(stream_in) & 7) return fail(CVXGPU_ERR_ARG, "compressed stream must be 8-byte aligned");
@@ -728,7 +735,8 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
     if (rc) return rc;
     const void* d_stream = stream_in;
     if (!in_dev) {
-        // the reference never reads compressed_length (CvxCompress.cpp:463-571); callers may pass 0
+        // the reference never reads compressed_length (CvxCompress.cpp:463-571): callers may pass 0 or garbage <= 0, and the
+        // extent of the stream then follows from its own tables
         long len = length;
         if (len <= 0) {
             len = derive_stream_length(stream_in);
@@ -744,7 +752,7 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
         }
         rc = reserve(&ws->d_stage_stream, &ws->stage_stream_bytes, (size_t)len + 64);
         if (rc) return rc;
-        rc = copy_chunked(ws->d_stage_stream, stream_in, (size_t)(len - 7 > 32 ? len - 7 : len), cudaMemcpyHostToDevice, st);
+        rc = cvx_stage_upload(ws, ws->d_stage_stream, stream_in, (size_t)(len - 7 > 32 ? len - 7 : len), st);
         if (rc) return rc;
         d_stream = ws->d_stage_stream;
     }
@@ -757,10 +765,7 @@ extern "C" int cvxgpu_decompress(float* vol, int nx, int ny, int nz, const void*
     }
     rc = decompress_with_header(ws, d_vol, nx, ny, nz, h, d_stream, length, st);
     if (rc) return rc;
-    if (!vol_dev) {
-        rc = copy_chunked(vol, d_vol, vol_bytes, cudaMemcpyDeviceToHost, st);
-        if (rc) return rc;
-    }
+    if (!vol_dev) return cvx_stage_download(ws, vol, d_vol, vol_bytes, st);
     CU(cudaStreamSynchronize(st));
     return CVXGPU_OK;
 }

@@ -32,9 +32,23 @@ struct cvxgpu_workspace {
     size_t stage_vol_bytes = 0;
     unsigned char* d_stage_stream = nullptr;
     size_t stage_stream_bytes = 0;
+    unsigned char* h_stage = nullptr;     // pinned bounce buffers of the staged pageable-memory copies (cvx_stage.cpp)
+    size_t h_stage_bytes = 0;
+    cudaStream_t priv_stream = nullptr;   // non-blocking stream of the host-pointer entry points (never the legacy stream 0)
 };
 
 int cvx_internal_default_ws(cvxgpu_workspace** out, void* cuda_stream);
+int cvx_stage_upload(cvxgpu_workspace* ws, void* d_dst, const void* h_src, size_t bytes, cudaStream_t st);
+int cvx_stage_download(cvxgpu_workspace* ws, void* h_dst, const void* d_src, size_t bytes, cudaStream_t st);
+
+// Device allocations made while some stream of the process is being captured into a CUDA graph: cudaMalloc is refused
+// in the (default) global capture mode, so the calling thread switches to the relaxed mode for the allocation alone
+// (cudaThreadExchangeStreamCaptureMode).  The memory is ordinary device memory that outlives the graph.
+struct CvxRelaxCapture {
+    cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+    CvxRelaxCapture() { cudaThreadExchangeStreamCaptureMode(&mode); }
+    ~CvxRelaxCapture() { cudaThreadExchangeStreamCaptureMode(&mode); }
+};
 
 namespace cvx {
 

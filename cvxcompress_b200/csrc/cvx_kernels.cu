@@ -78,7 +78,7 @@ __global__ void k_sumsq_finish(const double* __restrict__ partial, int n, double
 // slabs: the global RMS of a volume sharded over G GPUs must not depend on G, so every block row's sum
 // is formed by a fixed number of CTAs in a fixed order relative to the ROW start (no alignment peel: rows that do not
 // start on a 16-byte boundary take scalar loads into the same four accumulators), and the rows are added in row order.
-constexpr int SUMSQ_ROW_CTAS = 64;
+constexpr int SUMSQ_ROW_CTAS = 128;
 
 __global__ void __launch_bounds__(SUMSQ_T) k_sumsq_rows(const float* __restrict__ vol, long plane_cells, int bz, int nz,
                                                         double* __restrict__ partial)
@@ -88,19 +88,24 @@ __global__ void __launch_bounds__(SUMSQ_T) k_sumsq_rows(const float* __restrict_
     const int nzr = min(bz, nz - z0);
     const long n = plane_cells * nzr;
     const float* base = vol + plane_cells * (long)z0;
-    const long nthreads = (long)SUMSQ_ROW_CTAS * SUMSQ_T;
+    constexpr long NT = (long)SUMSQ_ROW_CTAS * SUMSQ_T;
     const long gtid = (long)blockIdx.x * SUMSQ_T + threadIdx.x;
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     const long n4 = n >> 2;
+    // element group g (4 cells) belongs to thread g mod NT and is added in increasing g: the order is a property of the
+    // row alone.  Four groups are in flight per thread (a slab of a few rows on one GPU still has to fill the HBM pipes).
     if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) {
         const float4* v4 = reinterpret_cast<const float4*>(base);
-        for (long i = gtid; i < n4; i += nthreads) {
-            const float4 q = __ldg(&v4[i]);
-            const double d0 = q.x, d1 = q.y, d2 = q.z, d3 = q.w;
-            a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
+        long i = gtid;
+        for (; i + 3 * NT < n4; i += 4 * NT) {
+            const float4 q0 = __ldg(&v4[i]), q1 = __ldg(&v4[i + NT]), q2 = __ldg(&v4[i + 2 * NT]), q3 = __ldg(&v4[i + 3 * NT]);
+#define CVX_ACC(q) { const double d0 = q.x, d1 = q.y, d2 = q.z, d3 = q.w; a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3; }
+            CVX_ACC(q0) CVX_ACC(q1) CVX_ACC(q2) CVX_ACC(q3)
         }
+        for (; i < n4; i += NT) { const float4 q = __ldg(&v4[i]); CVX_ACC(q) }
+#undef CVX_ACC
     } else {
-        for (long i = gtid; i < n4; i += nthreads) {
+        for (long i = gtid; i < n4; i += NT) {
             const double d0 = __ldg(base + 4 * i), d1 = __ldg(base + 4 * i + 1), d2 = __ldg(base + 4 * i + 2), d3 = __ldg(base + 4 * i + 3);
             a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
         }
@@ -852,6 +857,7 @@ bool make_volume_tmap(CUtensorMap* map, const void* d_vol, int nx, int ny, int n
 cudaError_t ws_reserve_status(cvxgpu_workspace* ws, long nblk)
 {
     if (nblk <= ws->status_cap) return cudaSuccess;
+    CvxRelaxCapture relax;
     if (ws->d_status) cudaFree(ws->d_status);
     ws->d_status = nullptr; ws->status_cap = 0;
     long cap = nblk + nblk / 4 + 1024;
@@ -863,6 +869,7 @@ cudaError_t ws_reserve_status(cvxgpu_workspace* ws, long nblk)
 cudaError_t ws_reserve_scratch(cvxgpu_workspace* ws, size_t bytes)
 {
     if (bytes <= ws->scratch_bytes) return cudaSuccess;
+    CvxRelaxCapture relax;
     if (ws->d_scratch) cudaFree(ws->d_scratch);
     ws->d_scratch = nullptr; ws->scratch_bytes = 0;
     cudaError_t e = cudaMalloc(&ws->d_scratch, bytes);
@@ -884,6 +891,7 @@ cudaError_t launch_sumsq(cvxgpu_workspace* ws, const float* d_vol, long ncells, 
 cudaError_t ws_reserve_rows(cvxgpu_workspace* ws, int rows)
 {
     if (rows <= ws->rows_cap) return cudaSuccess;
+    CvxRelaxCapture relax;
     if (ws->d_rowpartial) cudaFree(ws->d_rowpartial);
     if (ws->d_rowsum) cudaFree(ws->d_rowsum);
     ws->d_rowpartial = nullptr; ws->d_rowsum = nullptr; ws->rows_cap = 0;

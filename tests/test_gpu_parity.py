@@ -330,17 +330,24 @@ def test_sharded_pieces_on_one_gpu(gpu, world, case):
     """SURVEY.md 8(e) through the C-ABI pieces (cvxgpu_sumsq_device / encode_blocks / offsets / decode_blocks) with the
     ranks of a `world`-GPU job run one after the other on this GPU: the assembled stream equals the oracle's."""
     import torch
-    from cvxcompress_b200 import sharded
+    from cvxcompress_b200 import sharded, _lib
     kind, nx, ny, nz, bx, by, bz, scale, local = case
     vol = _vol(kind, nx, ny, nz)
     be = sharded.CudaBackend()
     geoms = [sharded.Geometry(nx, ny, nz, bx, by, bz, r, world) for r in range(world)]
     slabs = [torch.from_numpy(np.ascontiguousarray(vol[g.z0:g.z1])).cuda() for g in geoms]
-    # (1) per-rank sums of squares, added in rank order (what the all-gather + fixed-order sum does)
+    # (1) per-block-row sums of squares of every rank, concatenated in rank (= row) order and added one after the other
+    #     (what the all-gather + fixed-order sum does): the same arithmetic for every world size
     total = torch.zeros(1, dtype=torch.float64, device="cuda")
     if not local:
-        for s in slabs:
-            total += be.sumsq(s)
+        rows = torch.cat([be.sumsq_rows(s, g) for s, g in zip(slabs, geoms)])
+        assert rows.numel() == geoms[0].nbz
+        _lib.check(_lib.lib().cvxgpu_sum_rows_device(rows.data_ptr(), rows.numel(), total.data_ptr(), None))
+        whole = torch.zeros(1, dtype=torch.float64, device="cuda")
+        g1 = sharded.Geometry(nx, ny, nz, bx, by, bz, 0, 1)
+        rows1 = be.sumsq_rows(torch.from_numpy(np.ascontiguousarray(vol)).cuda(), g1)
+        _lib.check(_lib.lib().cvxgpu_sum_rows_device(rows1.data_ptr(), rows1.numel(), whole.data_ptr(), None))
+        assert torch.equal(rows, rows1) and torch.equal(total, whole)       # bit-identical for G = 1, 2, 3
     header = be.header(geoms[0], scale, local, total).cpu().numpy()
     # (2) per-rank encode, (3) bases from the payload sizes
     parts, base = [], 0
