@@ -613,6 +613,34 @@ def run_ours(args):
                       "decode_kernel_frac": (4 * cells_rank + stream_slab_bytes) / (tdo * 1e-3) / 1e9 / peak}
         api.set_transform(args.transform)
 
+    # -- what limits strong scaling: the fixed cost of a sharded call (kernel launches inside the graph, the two 8-byte..
+    #    ncclAllGather, the tail of a persistent grid), measured on a volume of one tiny block row per rank where the
+    #    kernels themselves take a few microseconds --
+    fixed = None
+    if world > 1:
+        tiny = torch.zeros((BZ, 64, 64), dtype=torch.float32, device=dev) + float(rank + 1)
+        tss = sharded.compress_slab(tiny, 64, 64, BZ * world, BX, BY, BZ, SCALE, LOCAL)
+        tout = torch.empty_like(tiny)
+        sharded.decompress_slab(tss, out=tout)
+        torch.cuda.synchronize()
+        gt = torch.cuda.CUDAGraph()
+        sst = torch.cuda.Stream()
+        sst.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.graph(gt, stream=sst):
+            tss = sharded.compress_slab(tiny, 64, 64, BZ * world, BX, BY, BZ, SCALE, LOCAL, out=tss)
+        torch.cuda.current_stream().wait_stream(sst)
+        barrier()
+        t_fix = time_kernel(gt.replay, 50)
+        barrier()
+        t_fix_eager = time_kernel(lambda: sharded.compress_slab(tiny, 64, 64, BZ * world, BX, BY, BZ, SCALE, LOCAL, out=tss), 50)
+        ksum = sum(v["ms"] for k, v in kern.items() if not k.startswith("k_decode"))
+        fixed = {"sharded_compress_of_a_64x64x%d_volume_ms" % (BZ * world): t_fix, "same_without_cuda_graph_ms": t_fix_eager,
+                 "compress_ms": tc_ms, "compress_kernels_ms": ksum, "compress_overhead_ms": tc_ms - ksum,
+                 "decompress_ms": td_ms, "decompress_kernel_ms": kern[dec_name]["ms"],
+                 "note": "overhead = whole sharded call minus its two hot kernels timed alone; the tiny-volume call is the floor of that overhead "
+                         "(launch gaps + 2 ncclAllGather of 8..%d bytes + the small kernels)" % (8 * max(1, -(-NZ // BZ // world)))}
+        del gt
+
     # -- a short weak-scaling run beside the strong one: every rank a full volume's worth of planes --
     weak = None
     if world > 1 and args.scaling == "strong":
@@ -659,7 +687,7 @@ def run_ours(args):
                     "" if LOCAL else "k_sumsq_rows, k_sumsq_rows_finish, k_sum_rows, ", enc_name,
                     "k_shard_fixup + 2 ncclAllGather" if world > 1 else "k_finish_length", "k_shard_extent, " if world > 1 else "", dec_name,
                     "; each direction replayed from one CUDA graph" if (world > 1 and not args.no_graph) else ""),
-                "exact_mode": exact_info, "weak": weak, "numa": numa}
+                "exact_mode": exact_info, "weak": weak, "strong_scaling_fixed_cost": fixed, "numa": numa}
         emit(line)
     if world > 1:
         dist.barrier()
