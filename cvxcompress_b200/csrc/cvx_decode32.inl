@@ -15,6 +15,7 @@
 
 constexpr int D32_T = 512;
 constexpr int D32_CH = 1024;                          // 8-byte chunks per window, two per thread
+constexpr int D32_MINWIN = 4080;                      // bytes of a first window parsed regardless of the table's length hint (+ <= 15 of misalignment: 512 chunks)
 constexpr int D32_WIN = D32_CH * 8 + 32;              // + look-ahead for tokens straddling the window end
 constexpr int D32_OFF_WIN = F32_B * 4;                // two windows
 constexpr int D32_OFF_EXT = D32_OFF_WIN + 2 * D32_WIN;
@@ -95,8 +96,13 @@ __device__ __forceinline__ D32Src d32_locate_finish(const DecParams& p, long t, 
     o &= 0x7FFFFFFFFFFFFFFFull;
     r.src = p.payload + o;
     long nxt = (t + 1 < p.nblk) ? (long)(w.o1 & 0x7FFFFFFFFFFFFFFFull) : p.payload_bytes;
-    long h = nxt - (long)o;
-    r.hint = (h > 0 && h <= 5L * F32_B + 8) ? h : 0;
+    // The table tells a block's payload length only when the blocks lie in natural order; a stream written by the
+    // reference with several threads has them permuted (CvxCompress.cpp:365-390) and the difference to the next entry is
+    // then meaningless (negative, tiny or huge).  So a first window of at least D32_MINWIN bytes is parsed whatever the
+    // table says: that is the same one (k_decode32) or two (k_decode32ws parser) chunks per thread a typical ~3 KiB
+    // payload takes anyway, and it serves a block of any order; a payload that turns out longer continues window by window.
+    const long h = nxt - (long)o;
+    r.hint = (h > D32_MINWIN && h <= D32_CH * 8 - 16) ? h : D32_MINWIN;
     const float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
     r.scalefac = __fdiv_rn(1.0f, mulfac);                        // Run_Length_Encode_Slow.cpp:392
     return r;

@@ -978,13 +978,14 @@ static cudaError_t launch_persistent(K kernel, int T, size_t smem, long nwork, i
     return cudaGetLastError();
 }
 
-// kernel configuration by block shape: a 64-long line needs 255 registers (T = 256); blocks of
+// kernel configuration by block shape: a 64-long line needs 255 registers in EXACT arithmetic (the level copy; T = 256,
+// one CTA per SM) but 64 + addressing in LIFTING (in place: 128 registers, two CTAs per SM); blocks of
 // >= 16384 cells use 512 threads (2 lines per thread and pass at 32^3); small blocks 128 threads
 #define CVX_DISPATCH_FUSED(CALL)                                         \
     do {                                                                 \
         const int maxn = s.bx > s.by ? (s.bx > s.bz ? s.bx : s.bz) : (s.by > s.bz ? s.by : s.bz); \
         const long cells = (long)s.bx * s.by * s.bz;                     \
-        if (maxn == 64) { if (exact) CALL(64, true, 256, 1); else CALL(64, false, 256, 1); }            \
+        if (maxn == 64) { if (exact) CALL(64, true, 256, 1); else CALL(64, false, 256, 2); }            \
         else if (cells >= 16384) { if (exact) CALL(32, true, 512, 1); else CALL(32, false, 512, 1); }   \
         else { if (exact) CALL(32, true, 128, 4); else CALL(32, false, 128, 4); }                        \
     } while (0)
