@@ -660,77 +660,10 @@ __global__ void __launch_bounds__(T, MINB) k_wavelet_fused(float* blocks, long n
 }
 
 // ------------------------------------------------------------------------------------------
-// Staged path (any valid block shape): blocks of a batch are dense arrays in global scratch.
-// EXACT arithmetic only.  One thread owns one line; y/z lines are coalesced across lanes (lane =
-// x), x lines are read by one thread each (L1/L2 absorb the 4*bx-byte rows).
+// Large-block path (any dimension > 64, or more than 32768 cells): blocks of a batch are dense arrays in global
+// scratch; the three line passes are cvx_bigblock.inl, the coder / parser below work on the scratch blocks.
 // ------------------------------------------------------------------------------------------
-struct StageParams {
-    float* scratch;        // nb dense blocks
-    long blk_first;        // first block (ticket) of the batch
-    int nb;                // blocks in the batch
-    BlkShape s;
-    int nbx, nby;
-    VolView g;
-};
-
-__global__ void k_stage_gather(const float* __restrict__ vol, const StageParams p)
-{
-    const long B = p.s.B;
-    const long total = (long)p.nb * B;
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const long k = i / B;
-        const long c = i - k * B;
-        const long t = p.blk_first + k;
-        const int iix = (int)(t % p.nbx);
-        const long q = t / p.nbx;
-        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
-        const int x = (int)(c & (p.s.bx - 1));
-        const long r = c >> p.s.lbx;
-        const int gy = iiy * p.s.by + (int)(r & (p.s.by - 1)), gz = iiz * p.s.bz + (int)(r >> p.s.lby), gx = iix * p.s.bx + x;
-        float v = 0.f;
-        if (gx < p.g.nx && gy < p.g.ny && gz < p.g.nz) v = __ldg(vol + ((long)gz * p.g.ny + gy) * p.g.nx + gx);
-        p.scratch[i] = v;
-    }
-}
-
-__global__ void k_stage_scatter(float* __restrict__ vol, const StageParams p)
-{
-    const long B = p.s.B;
-    const long total = (long)p.nb * B;
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const long k = i / B;
-        const long c = i - k * B;
-        const long t = p.blk_first + k;
-        const int iix = (int)(t % p.nbx);
-        const long q = t / p.nbx;
-        const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
-        const int x = (int)(c & (p.s.bx - 1));
-        const long r = c >> p.s.lbx;
-        const int gy = iiy * p.s.by + (int)(r & (p.s.by - 1)), gz = iiz * p.s.bz + (int)(r >> p.s.lby), gx = iix * p.s.bx + x;
-        if (gx < p.g.nx && gy < p.g.ny && gz < p.g.nz) vol[((long)gz * p.g.ny + gy) * p.g.nx + gx] = p.scratch[i];
-    }
-}
-
-// axis 0: x, 1: y, 2: z.  All levels of one line per thread.
-template <bool FWD>
-__global__ void __launch_bounds__(128) k_stage_pass(float* scratch, int nb, const BlkShape s, int axis)
-{
-    const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
-    const long lines_per_blk = s.B / n;
-    const long total = (long)nb * lines_per_blk;
-    float tmp[256];
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const long k = i / lines_per_blk;
-        const long l = i - k * lines_per_blk;
-        float* blk = scratch + k * (long)s.B;
-        long base, stride;
-        if (axis == 0) { base = l * s.bx; stride = 1; }
-        else if (axis == 1) { base = (l >> s.lbx) * ((long)s.bx * s.by) + (l & (s.bx - 1)); stride = s.bx; }
-        else { base = l; stride = (long)s.bx * s.by; }
-        if (FWD) fwd_exact_mem(blk + base, stride, tmp, n);
-        else inv_exact_mem(blk + base, stride, tmp, n);
-    }
-}
+#include "cvx_bigblock.inl"
 
 constexpr int STAGE_T = 512;
 
@@ -747,7 +680,7 @@ __global__ void __launch_bounds__(STAGE_T, 1) k_stage_encode(const EncParams p, 
         const float* coef = scratch + (long)k * p.s.B;
         float mulfac = gmul;
         if (p.use_local) {
-            // the staged path is EXACT arithmetic throughout: the reference's summation order
+            // large-block path: always the reference's summation order (the multiplier travels in the stream)
             float ss = cta_sumsq_exact<STAGE_T>(p.s.B, s_red, [&](int i) { return __ldg(coef + i); });
             float rms = sqrtf(__fdiv_rn(ss, (float)p.s.B));
             mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
@@ -1059,18 +992,11 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
     if (e != cudaSuccess) return e;
     for (long b0 = 0; b0 < s.nblk; b0 += per_batch) {
         const int nb = (int)((s.nblk - b0) < per_batch ? (s.nblk - b0) : per_batch);
-        StageParams sp;
-        sp.scratch = ws->d_scratch; sp.blk_first = b0; sp.nb = nb; sp.s = p.s; sp.nbx = s.nbx; sp.nby = s.nby; sp.g = p.g;
-        const long cells = (long)nb * p.s.B;
-        const unsigned g1 = (unsigned)((cells + 255) / 256 < 148L * 64 ? (cells + 255) / 256 : 148L * 64);
-        k_stage_gather<<<g1, 256, 0, st>>>(d_vol, sp);
-        for (int axis = 0; axis < 3; ++axis) {
-            const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
-            if (n < 2) continue;
-            const long lines = cells / n;
-            const unsigned g2 = (unsigned)((lines + 127) / 128);
-            k_stage_pass<true><<<g2, 128, 0, st>>>(ws->d_scratch, nb, p.s, axis);
-        }
+        BigParams bp;
+        bp.scratch = ws->d_scratch; bp.blk_first = b0; bp.nb = nb; bp.s = p.s; bp.nbx = s.nbx; bp.nby = s.nby; bp.g = p.g;
+        bp.vol_in = d_vol; bp.vol_out = nullptr;
+        e = launch_big_transform(bp, true, exact != 0, ws->sm_count, st);         // gather fused into the x pass
+        if (e != cudaSuccess) return e;
         const int ge = nb < ws->sm_count ? nb : ws->sm_count;
         k_stage_encode<<<ge, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
         e = cudaGetLastError();
@@ -1129,18 +1055,11 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
         const int nb = (int)((s.nblk - b0) < per_batch ? (s.nblk - b0) : per_batch);
         const int gd = nb < ws->sm_count * 2 ? nb : ws->sm_count * 2;
         k_stage_decode<<<gd, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
-        const long cells = (long)nb * p.s.B;
-        for (int axis = 0; axis < 3; ++axis) {
-            const int n = axis == 0 ? s.bx : axis == 1 ? s.by : s.bz;
-            if (n < 2) continue;
-            const long lines = cells / n;
-            const unsigned g2 = (unsigned)((lines + 127) / 128);
-            k_stage_pass<false><<<g2, 128, 0, st>>>(ws->d_scratch, nb, p.s, axis);
-        }
-        StageParams sp;
-        sp.scratch = ws->d_scratch; sp.blk_first = b0; sp.nb = nb; sp.s = p.s; sp.nbx = s.nbx; sp.nby = s.nby; sp.g = p.g;
-        const unsigned g1 = (unsigned)((cells + 255) / 256 < 148L * 64 ? (cells + 255) / 256 : 148L * 64);
-        k_stage_scatter<<<g1, 256, 0, st>>>(d_vol, sp);
+        BigParams bp;
+        bp.scratch = ws->d_scratch; bp.blk_first = b0; bp.nb = nb; bp.s = p.s; bp.nbx = s.nbx; bp.nby = s.nby; bp.g = p.g;
+        bp.vol_in = nullptr; bp.vol_out = d_vol;
+        e = launch_big_transform(bp, false, exact != 0, ws->sm_count, st);        // scatter fused into the last pass
+        if (e != cudaSuccess) return e;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -1165,20 +1084,15 @@ cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, 
 #undef CVX_CALL_WAV
         return e;
     }
-    // staged, in place on the caller's dense blocks, in batches that keep the int block count small
+    // large blocks: the three line passes in place on the caller's dense blocks, in batches that keep the int block count small
     const long per_batch = 1 << 20;
     for (long b0 = 0; b0 < nblocks; b0 += per_batch) {
         const int nb = (int)((nblocks - b0) < per_batch ? (nblocks - b0) : per_batch);
-        const long cells = (long)nb * b.B;
-        for (int axis = 0; axis < 3; ++axis) {
-            const int n = axis == 0 ? bx : axis == 1 ? by : bz;
-            if (n < 2) continue;
-            const long lines = cells / n;
-            const unsigned g2 = (unsigned)((lines + 127) / 128);
-            if (inverse) k_stage_pass<false><<<g2, 128, 0, st>>>(d_blocks + b0 * b.B, nb, b, axis);
-            else k_stage_pass<true><<<g2, 128, 0, st>>>(d_blocks + b0 * b.B, nb, b, axis);
-        }
-        e = cudaGetLastError();
+        BigParams bp;
+        bp.scratch = d_blocks + b0 * b.B; bp.blk_first = 0; bp.nb = nb; bp.s = b; bp.nbx = 1; bp.nby = 1;
+        bp.g.nx = bx; bp.g.ny = by; bp.g.nz = bz; bp.g.vec_ok = 1;
+        bp.vol_in = nullptr; bp.vol_out = nullptr;
+        e = launch_big_transform(bp, !inverse, exact != 0, ws->sm_count, st);
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;

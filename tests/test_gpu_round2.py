@@ -307,3 +307,69 @@ def test_reference_driver_relinked_against_this_library(gpu):
     assert lens == [178789, 1430039, 4826289], r.stdout[-2000:]
     snrs = [float(x) for x in re.findall(r"SNR = ([0-9.]+) dB", r.stdout)]
     assert len(snrs) == 3 and all(abs(s - 75.6) < 0.05 for s in snrs), snrs
+
+
+# ---- large blocks (64^3 .. 256^3 and anisotropic shapes with a 128 / 256 side): cvx_bigblock.inl ----------------------
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("shape", [(64, 64, 64), (128, 128, 128), (256, 256, 256), (256, 8, 16), (8, 128, 64), (128, 128, 1), (16, 64, 256)],
+                         ids=lambda s: "%dx%dx%d" % s)
+def test_large_blocks_full_pipeline(gpu, shape):
+    """Cubes the reference publishes throughput for (README.md:38-40) and shapes whose lines run in shared memory
+    (128, 256): EXACT byte-identical to the oracle; LIFTING decodes with the oracle to the same volume within the LIFTING
+    tolerance, at the same ratio and SNR."""
+    import torch
+    api = gpu
+    bx, by, bz = shape
+    nx, ny, nz = 200, 136, (1 if bz == 1 else 144)
+    if bx * by * bz >= 128 ** 3:
+        nx, ny, nz = 300, 260, 270                      # 2 x 2 x 2 (128^3) or 2 x 2 x 2 partial (256^3) blocks
+    vol = synth.g2(nx, ny, nz)
+    d = torch.from_numpy(vol).cuda()
+    want, _ = ol.oracle_compress(vol, bx, by, bz, 1e-2)
+    ref = ol.oracle_decompress(want, nx, ny, nz)
+    s, ln, _ = api.compress_device(d, bx, by, bz, 1e-2)
+    assert _streams_equal(s[:ln].cpu().numpy(), want)
+    rec = api.decompress_device(s, ln, nx, ny, nz).cpu().numpy()
+    assert np.array_equal(rec.view(np.uint32), ref.view(np.uint32))
+    api.set_transform("lifting")
+    s2, ln2, _ = api.compress_device(d, bx, by, bz, 1e-2)
+    assert abs(ln2 - ln) <= 0.005 * ln
+    rec2 = api.decompress_device(s2, ln2, nx, ny, nz).cpu().numpy()
+    ref2 = ol.oracle_decompress(s2[:ln2].cpu().numpy(), nx, ny, nz)
+    assert np.max(np.abs(rec2 - ref2)) <= 2e-5 * np.max(np.abs(vol))
+    e1, snr1 = synth.quality(vol, ref)
+    e2, snr2 = synth.quality(vol, rec2)
+    assert abs(snr1 - snr2) < 0.1
+    # local RMS through the same path
+    s3, ln3, _ = api.compress_device(d, bx, by, bz, 1e-2, True)
+    ref3 = ol.oracle_decompress(s3[:ln3].cpu().numpy(), nx, ny, nz)
+    rec3 = api.decompress_device(s3, ln3, nx, ny, nz).cpu().numpy()
+    assert np.max(np.abs(rec3 - ref3)) <= 2e-5 * np.max(np.abs(vol))
+
+
+@pytest.mark.parametrize("shape", [(64, 64, 64), (128, 128, 128), (256, 256, 256), (256, 16, 8)], ids=lambda s: "%dx%dx%d" % s)
+@pytest.mark.parametrize("mode", ["exact", "lifting"])
+def test_large_block_wavelet_only(gpu, shape, mode):
+    """cvxgpu_wavelet_blocks_device on large dense blocks: EXACT bit-identical to the oracle's transform, LIFTING within
+    1e-5 rms-relative (the reference's own Fast-vs-Slow criterion, CvxCompress.cpp:597); forward + inverse returns the input."""
+    import torch
+    api = gpu
+    bx, by, bz = shape
+    n = bx * by * bz
+    nblk = 3 if n <= 128 ** 3 else 2
+    src = synth.g3(n * nblk, seed=11, lo=-1.0, hi=1.0)
+    want = src.copy().reshape(nblk, n)
+    for k in range(nblk):
+        ol.oracle().cvxo_wavelet_forward(want[k], bx, by, bz, 0)
+    api.set_transform(mode)
+    d = torch.from_numpy(src).cuda().view(nblk, bz, by, bx)
+    api.wavelet_blocks_device(d, bx, by, bz, inverse=False)
+    got = d.cpu().numpy().reshape(nblk, n)
+    if mode == "exact":
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    else:
+        rel = np.sqrt(np.mean((got.astype(np.float64) - want) ** 2) / np.mean(want.astype(np.float64) ** 2))
+        assert rel < 1e-5, rel
+    api.wavelet_blocks_device(d, bx, by, bz, inverse=True)
+    back = d.cpu().numpy().reshape(-1)
+    assert np.max(np.abs(back - src)) < 1e-5
