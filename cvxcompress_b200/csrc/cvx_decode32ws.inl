@@ -2,8 +2,8 @@
 //
 // The fused decoder's phases each saturate ONE pipe -- the token parse the (half-rate) integer pipe, the line
 // transforms the FMA pipe, the row stores the load/store unit -- and in k_decode32 they run one after the other.
-// Here a CTA has 20 warps: warps 0..15 (the transform group) run expand -> x -> y -> z -> store of block t while
-// warps 16..19 (the parser group) turn block t+1's payload into a compact (raster index, value) list, so the
+// Here a CTA has 24 warps: warps 0..15 (the transform group) run expand -> x -> y -> z -> store of block t while
+// warps 16..23 (the parser group) turn the next blocks' payloads (up to two ahead: two list buffers) into compact (raster index, value) lists, so the
 // integer work of one block overlaps the floating-point work of its predecessor.
 //   parser:    payload window (cp.async) -> contiguous chunk ranges per thread (speculation only at the range start,
 //              exact state inside it) -> chain check over 128 threads -> value / entry counts -> scan -> list
@@ -15,18 +15,18 @@
 constexpr int W32_TT = 512;                          // transform threads (warps 0..15)
 constexpr int W32_PT = 256;                          // parser threads (warps 16..19)
 constexpr int W32_T = W32_TT + W32_PT;
-constexpr int W32_LCAP = 6144;                       // list entries (8 bytes each)
+constexpr int W32_LCAP = 4096;                       // entries (8 bytes each) of each of the TWO lists: the parser may run two blocks ahead
 constexpr int W32_OFF_WIN = F32_B * 4;               // two parser windows, then the in-line window
 constexpr int W32_OFF_EXT = W32_OFF_WIN + 3 * D32_WIN;
 constexpr int W32_OFF_MASK = W32_OFF_EXT + D32_CH * 4;          // uint8[1024] token-start masks of the parser
 constexpr int W32_OFF_LIST = W32_OFF_MASK + D32_CH;
-constexpr int W32_SMEM = W32_OFF_LIST + W32_LCAP * 8;           // 210 048 bytes
+constexpr int W32_SMEM = W32_OFF_LIST + 2 * W32_LCAP * 8;       // 226 432 bytes
 
 typedef NamedBar<1, W32_TT> TBar;                    // transform group
 typedef NamedBar<2, W32_PT> PBar;                    // parser group
 __device__ __forceinline__ void w32_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(W32_T) : "memory"); }
 __device__ __forceinline__ void w32_wait(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(W32_T) : "memory"); }
-constexpr int W32_BAR_FULL = 3, W32_BAR_EMPTY = 4;
+constexpr int W32_BAR_FULL = 3, W32_BAR_EMPTY = 5;   // + list buffer index (0 / 1)
 
 #ifdef CVX_PHASE_TIMING
 #define W32_PH_DECL long long ph_last = clock64(); unsigned long long ph_acc[12] = {0}
@@ -164,10 +164,10 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
     unsigned char* s_win = smem_raw + W32_OFF_WIN;
     int* s_ext = reinterpret_cast<int*>(smem_raw + W32_OFF_EXT);
     unsigned char* s_mask = smem_raw + W32_OFF_MASK;
-    uint2* s_list = reinterpret_cast<uint2*>(smem_raw + W32_OFF_LIST);
+    uint2* s_lists = reinterpret_cast<uint2*>(smem_raw + W32_OFF_LIST);
     __shared__ unsigned long long scratch64[W32_TT / 32];
     __shared__ unsigned long long pscratch64[W32_PT / 32];
-    __shared__ int s_ctl[2];                                       // [0] entries in the list, or -1: decode in line
+    __shared__ int s_ctl[2];                                       // per list buffer: entries in the list, or -1: decode in line
     __shared__ int p_ext[W32_PT];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -214,18 +214,19 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
             asm volatile("cp.async.wait_group 1;" ::: "memory");   // this block's window has landed (this thread's part ...
             PBar::sync();                                          // ... and everybody else's)
             W32_PH(6);
-            if (it > 0) w32_wait(W32_BAR_EMPTY);                   // the previous list has been scattered
+            const int lb = it & 1;
+            if (it >= 2) w32_wait(W32_BAR_EMPTY + lb);             // the list written two blocks ago has been scattered
             W32_PH(7);
-            if (servable) n = w32_parse_to_list(b, win, s_mask, p_ext, pscratch64, s_list);
-            if (ptid == 0) s_ctl[0] = n;
+            if (servable) n = w32_parse_to_list(b, win, s_mask, p_ext, pscratch64, s_lists + lb * W32_LCAP);
+            if (ptid == 0) s_ctl[lb] = n;
             __threadfence_block();
             PBar::sync();                                          // every parser thread is done with the window: the next load may overwrite it
-            w32_arrive(W32_BAR_FULL);
+            w32_arrive(W32_BAR_FULL + lb);
             b = bn;
             W32_PH(8);
         }
         W32_PH_FLUSH;
-        if (it > 0) w32_wait(W32_BAR_EMPTY);                       // match the transform group's last arrival
+        for (int k = it >= 2 ? it - 2 : 0; k < it; ++k) w32_wait(W32_BAR_EMPTY + (k & 1));     // match the transform group's last arrivals
         return;
     }
     // ------------------------------ transform group ------------------------------
@@ -238,11 +239,13 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
     }
     unsigned char* win2 = s_win + 2 * D32_WIN;                      // window of the in-line path
     CVX_PH_DECL;
-    for (long t = blockIdx.x; t < p.nblk; t += gridDim.x) {
+    int tb = 0;                                                     // list buffer of the block at hand
+    for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, tb ^= 1) {
         CVX_PH(5);
-        w32_wait(W32_BAR_FULL);                                     // also orders every thread's zeroing before the scatter
+        w32_wait(W32_BAR_FULL + tb);                                // also orders every thread's zeroing before the scatter
         CVX_PH(0);
-        const int n = s_ctl[0];
+        const int n = s_ctl[tb];
+        const uint2* s_list = s_lists + tb * W32_LCAP;
         if (n >= 0) {
             for (int i = tid; i < n; i += W32_TT) {
                 const uint2 e = s_list[i];
@@ -275,7 +278,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
             }
         }
         TBar::sync();                                               // block complete, s_ctl and the list consumed
-        w32_arrive(W32_BAR_EMPTY);
+        w32_arrive(W32_BAR_EMPTY + tb);
         CVX_PH(1);
         f32_pass_xT<EXACT, false, W32_TT>(sm, true);
         __syncwarp();

@@ -3,7 +3,15 @@ codes that checkpoint wavefields already resident in HBM, which the reference's 
 cannot serve.
 
     stream, length = torch.ops.cvx.compress(vol, bx, by, bz, scale, use_local_rms)
+    length         = torch.ops.cvx.compress_into(vol, bx, by, bz, scale, use_local_rms, out)     # caller-sized buffer
     vol            = torch.ops.cvx.decompress(stream, nx, ny, nz)
+    vol            = torch.ops.cvx.decompress_known(stream, nx, ny, nz, bx, by, bz, use_local_rms)   # no host sync
+
+`compress` allocates the worst case (every block raw: more than the volume itself); a checkpoint loop that knows its data
+passes its own buffer to `compress_into` -- a quarter of the volume is ample for seismic wavefields -- and an overflow
+comes back as a negative length, nothing is written past the buffer.  `decompress_known` takes the header fields from the
+caller instead of reading the stream's first 32 bytes back, so the decode side is free of host synchronisation too and
+both directions can be captured in one CUDA graph.
 
 Both are stream-ordered on torch's current CUDA stream.  `compress` does not synchronise with the host: `length` is a
 1-element int64 CUDA tensor (compressed_length, CvxCompress.cpp:421-422; negative = cvxgpu error code, e.g. the stream did
@@ -19,6 +27,8 @@ from . import _lib, api
 _lib_def = torch.library.Library("cvx", "DEF")
 _lib_def.define("compress(Tensor vol, int bx, int by, int bz, float scale, bool use_local_rms) -> (Tensor, Tensor)")
 _lib_def.define("decompress(Tensor stream, int nx, int ny, int nz) -> Tensor")
+_lib_def.define("compress_into(Tensor vol, int bx, int by, int bz, float scale, bool use_local_rms, Tensor(a!) out) -> Tensor")
+_lib_def.define("decompress_known(Tensor stream, int nx, int ny, int nz, int bx, int by, int bz, bool use_local_rms) -> Tensor")
 
 
 def _check_vol(vol):
@@ -42,6 +52,33 @@ def _compress_cuda(vol, bx, by, bz, scale, use_local_rms):
     return out, d_length
 
 
+def _compress_into_cuda(vol, bx, by, bz, scale, use_local_rms, out):
+    _check_vol(vol)
+    if out.dtype != torch.uint8 or out.dim() != 1 or not out.is_contiguous() or out.data_ptr() % 8:
+        raise ValueError("cvx::compress_into: out must be a contiguous, 8-byte aligned 1-D uint8 tensor")
+    vol = vol.contiguous()
+    nz, ny, nx = vol.shape
+    if api.max_compressed_bytes(nx, ny, nz, bx, by, bz, use_local_rms) < 0:
+        raise ValueError("cvx::compress_into: invalid block size %dx%dx%d" % (bx, by, bz))
+    d_length = torch.zeros(1, dtype=torch.int64, device=vol.device)
+    d_status = torch.zeros(1, dtype=torch.int32, device=vol.device)
+    api.compress_device_async(vol, bx, by, bz, scale, use_local_rms, out, d_length, d_status)
+    return torch.where(d_status != 0, d_status.to(torch.int64), d_length)
+
+
+def _decompress_known_cuda(stream, nx, ny, nz, bx, by, bz, use_local_rms):
+    import ctypes as C
+    if stream.dtype != torch.uint8 or stream.dim() != 1:
+        raise ValueError("cvx::decompress_known: stream must be a 1-D uint8 tensor")
+    stream = stream.contiguous()
+    out = torch.empty((nz, ny, nx), dtype=torch.float32, device=stream.device)
+    with torch.cuda.device(stream.device):
+        _lib.check(_lib.lib().cvxgpu_decompress_slab_device(
+            None, out.data_ptr(), nx, ny, nz, bx, by, bz, int(bool(use_local_rms)), 0, 1, stream.data_ptr(), stream.numel(),
+            C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
 def _decompress_cuda(stream, nx, ny, nz):
     if stream.dtype != torch.uint8 or stream.dim() != 1:
         raise ValueError("cvx::decompress: stream must be a 1-D uint8 tensor")
@@ -56,6 +93,10 @@ def _no_cpu(*args, **kwargs):
 _lib_impl = torch.library.Library("cvx", "IMPL")
 _lib_impl.impl("compress", _compress_cuda, "CUDA")
 _lib_impl.impl("decompress", _decompress_cuda, "CUDA")
+_lib_impl.impl("compress_into", _compress_into_cuda, "CUDA")
+_lib_impl.impl("decompress_known", _decompress_known_cuda, "CUDA")
+_lib_impl.impl("compress_into", _no_cpu, "CPU")
+_lib_impl.impl("decompress_known", _no_cpu, "CPU")
 _lib_impl.impl("compress", _no_cpu, "CPU")
 _lib_impl.impl("decompress", _no_cpu, "CPU")
 
@@ -70,4 +111,15 @@ def _compress_fake(vol, bx, by, bz, scale, use_local_rms):
 
 @torch.library.register_fake("cvx::decompress")
 def _decompress_fake(stream, nx, ny, nz):
+    return stream.new_empty((nz, ny, nx), dtype=torch.float32)
+
+
+@torch.library.register_fake("cvx::compress_into")
+def _compress_into_fake(vol, bx, by, bz, scale, use_local_rms, out):
+    _check_vol(vol)
+    return vol.new_empty(1, dtype=torch.int64)
+
+
+@torch.library.register_fake("cvx::decompress_known")
+def _decompress_known_fake(stream, nx, ny, nz, bx, by, bz, use_local_rms):
     return stream.new_empty((nz, ny, nx), dtype=torch.float32)

@@ -89,3 +89,40 @@ def test_compress_op_replays_in_a_cuda_graph():
         want, _ = ol.oracle_compress(vol.cpu().numpy(), 32, 32, 32, 1e-2, False)
         ln = int(length.item())
         assert ln == len(want) and bytes(stream[:ln - 7].cpu().numpy()) == bytes(want[:-7])
+
+
+@pytest.mark.gpu
+def test_round_trip_in_one_cuda_graph_with_caller_sized_buffer():
+    """compress_into (a buffer of a quarter of the volume, not the worst case) + decompress_known (header by value): neither
+    synchronises with the host, so a whole checkpoint round trip replays from one CUDA graph."""
+    api.set_transform("exact")
+    nx, ny, nz = 96, 64, 64
+    a = torch.from_numpy(synth.g2(nx, ny, nz)).cuda()
+    b = torch.from_numpy(synth.g2(nx, ny, nz)[::-1].copy()).cuda()
+    static_in = a.clone()
+    buf = torch.empty(a.numel() + 4096, dtype=torch.uint8, device="cuda")      # N bytes: a quarter of the volume
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        torch.ops.cvx.compress_into(static_in, 32, 32, 32, 1e-2, False, buf)
+        torch.ops.cvx.decompress_known(buf, nx, ny, nz, 32, 32, 32, False)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        length = torch.ops.cvx.compress_into(static_in, 32, 32, 32, 1e-2, False, buf)
+        back = torch.ops.cvx.decompress_known(buf, nx, ny, nz, 32, 32, 32, False)
+    for vol in (a, b):
+        static_in.copy_(vol)
+        g.replay()
+        torch.cuda.synchronize()
+        want, _ = ol.oracle_compress(vol.cpu().numpy(), 32, 32, 32, 1e-2, False)
+        ln = int(length.item())
+        assert ln == len(want) and bytes(buf[:ln - 7].cpu().numpy()) == bytes(want[:-7])
+        ref = ol.oracle_decompress(want, nx, ny, nz)
+        assert np.array_equal(back.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+    # a buffer that is too small: negative length (CVXGPU_ERR_CAPACITY), nothing written past it
+    small = torch.zeros(4096 + 64, dtype=torch.uint8, device="cuda")
+    guard = small[4096:].clone()
+    ln = torch.ops.cvx.compress_into(a, 32, 32, 32, 1e-2, False, small[:4096])
+    assert int(ln.item()) == -3 and torch.equal(small[4096:], guard)
