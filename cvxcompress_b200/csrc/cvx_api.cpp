@@ -279,8 +279,7 @@ extern "C" int cvxgpu_encode_blocks_device(cvxgpu_workspace* wsin, const float* 
         return fail(CVXGPU_ERR_ARG, "cvxgpu_encode_blocks_device: null pointer");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     Shape s = make_shape(nx, ny, nz_slab, bx, by, bz);
-    CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
-    CU(launch_write_header(nullptr, s, scale, local, d_sumsq_total, ncells_total, ws->d_mulfac, st));
+    CU(launch_write_header(nullptr, s, scale, local, d_sumsq_total, ncells_total, ws->d_mulfac, st));      // launch_encode clears *d_status
     CU(launch_encode(ws, d_vol, s, scale, local, ws->d_mulfac, d_offs, d_blkmulfac, d_payload, payload_capacity,
                      d_payload_bytes, d_status, exact_mode(), st));
     return CVXGPU_OK;
@@ -329,14 +328,9 @@ static int compress_enqueue(cvxgpu_workspace* ws, const float* d_vol, const Shap
     float* d_bmf = local ? reinterpret_cast<float*>(base + 32 + 8 * s.nblk) : nullptr;     // :308
     unsigned char* d_payload = base + 32 + tables;                                          // :309 / :314
     const long ncells = (long)s.nx * s.ny * s.nz;
-    CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
-    if (!local) {
-        // per-block-row sums added in row order: the same arithmetic the sharded path performs for any number of GPUs
-        const int rows = s.nbz;
-        CU(launch_sumsq_rows(ws, d_vol, (long)s.nx * s.ny, s.bz, s.nz, nullptr, st));
-        CU(launch_sum_rows(ws->d_rowsum, 0, 0, nullptr, rows, ws->d_sumsq, st));
-    }
-    CU(launch_write_header(d_stream, s, scale, local, ws->d_sumsq, ncells, ws->d_mulfac, st));
+    // per-block-row sums added in row order: the same arithmetic the sharded path performs for any number of GPUs
+    if (!local) CU(launch_sumsq_rows(ws, d_vol, (long)s.nx * s.ny, s.bz, s.nz, nullptr, st));
+    CU(launch_rms_header(local ? nullptr : ws->d_rowsum, 0, 0, nullptr, s.nbz, ws->d_sumsq, d_stream, s, scale, local, ncells, ws->d_mulfac, st));
     CU(launch_encode(ws, d_vol, s, scale, local, ws->d_mulfac, d_offs, d_bmf, d_payload, capacity - 32 - tables - 7,
                      ws->d_payload_bytes, d_status, exact_mode(), st));
     CU(launch_finish_length(ws->d_payload_bytes, tables, d_length, st));

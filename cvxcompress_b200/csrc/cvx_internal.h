@@ -70,6 +70,9 @@ cudaError_t launch_sumsq(cvxgpu_workspace* ws, const float* d_vol, long ncells, 
 cudaError_t ws_reserve_rows(cvxgpu_workspace* ws, int rows);
 cudaError_t launch_sumsq_rows(cvxgpu_workspace* ws, const float* d_vol, long plane_cells, int bz, int nz, double* d_rowsum, cudaStream_t st);
 cudaError_t launch_sum_rows(const double* d_rows, int nseg, int seg, const int* d_cnt, int n_single, double* d_total, cudaStream_t st);
+cudaError_t launch_rms_header(const double* d_rows, int nseg, int seg, const int* d_cnt, int n_single, double* d_sumsq,
+                              void* d_stream, const Shape& s, float scale, int use_local, long ncells_total, float* d_mulfac_out,
+                              cudaStream_t st);
 cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int use_local, const double* d_sumsq,
                                 long ncells_total, float* d_mulfac_out, cudaStream_t st);
 cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape& s, float scale, int use_local,

@@ -176,6 +176,41 @@ __global__ void k_write_header(int32_t* hdr, int nx, int ny, int nz, int bx, int
     }
 }
 
+// k_sum_rows and k_write_header in one launch (one graph node, one kernel-to-kernel latency less per Compress): the row
+// sums are added in row order, then the header and glob_mulfac follow from the total.  rows == nullptr: the total is
+// already in *sumsq (local RMS: not read at all).
+__global__ void k_rms_header(const double* __restrict__ rows, int nseg, int seg, const int* __restrict__ cnt, int n_single,
+                             double* __restrict__ sumsq, int32_t* hdr, int nx, int ny, int nz, int bx, int by, int bz, float scale,
+                             int use_local, long ncells, float* mulfac_out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (rows && !use_local) {
+        double s = 0.0;
+        if (nseg <= 0) {
+            for (int i = 0; i < n_single; ++i) s += rows[i];
+        } else {
+            for (int r = 0; r < nseg; ++r)
+                for (int i = 0; i < cnt[r]; ++i) s += rows[(long)r * seg + i];
+        }
+        *sumsq = s;
+    }
+    const float m = glob_mulfac_of(sumsq, ncells, scale, use_local);
+    if (hdr) {
+        hdr[0] = nx; hdr[1] = ny; hdr[2] = nz; hdr[3] = bx; hdr[4] = by; hdr[5] = bz;
+        hdr[6] = __float_as_int(m);
+        hdr[7] = use_local ? 1 : 0;
+    }
+    if (mulfac_out) *mulfac_out = m;
+}
+
+// everything an encode launch needs cleared, in one launch: the look-back words, the ticket, the status word and the byte count
+__global__ void k_encode_prep(unsigned long long* __restrict__ status, long nblk, unsigned int* ticket, int* err, long* payload_bytes)
+{
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nblk) status[i] = 0ull;
+    if (i == 0) { *ticket = 0u; if (err) *err = 0; if (payload_bytes) *payload_bytes = 0; }
+}
+
 __global__ void k_offsets_add(unsigned long long* offs, long n, unsigned long long base)
 {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -861,6 +896,15 @@ cudaError_t launch_sum_rows(const double* d_rows, int nseg, int seg, const int* 
     return cudaGetLastError();
 }
 
+cudaError_t launch_rms_header(const double* d_rows, int nseg, int seg, const int* d_cnt, int n_single, double* d_sumsq,
+                              void* d_stream, const Shape& s, float scale, int use_local, long ncells_total, float* d_mulfac_out,
+                              cudaStream_t st)
+{
+    k_rms_header<<<1, 32, 0, st>>>(d_rows, nseg, seg, d_cnt, n_single, d_sumsq, reinterpret_cast<int32_t*>(d_stream), s.nx, s.ny, s.nz,
+                                   s.bx, s.by, s.bz, scale, use_local, ncells_total, d_mulfac_out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_write_header(void* d_stream, const Shape& s, float scale, int use_local, const double* d_sumsq,
                                 long ncells_total, float* d_mulfac_out, cudaStream_t st)
 {
@@ -947,9 +991,9 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
 {
     cudaError_t e = ws_reserve_status(ws, s.nblk);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(ws->d_status, 0, sizeof(unsigned long long) * (size_t)s.nblk, st);
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(ws->d_ticket, 0, sizeof(unsigned int), st);
+    // look-back words, ticket, the caller's status word and byte count: cleared by one launch
+    k_encode_prep<<<(unsigned)((s.nblk + 255) / 256), 256, 0, st>>>(ws->d_status, s.nblk, ws->d_ticket, d_err, d_payload_bytes);
+    e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     EncParams p;
     p.vol = d_vol; p.g = vol_view(s, d_vol); p.s = blk_shape(s); p.nbx = s.nbx; p.nby = s.nby; p.nblk = s.nblk;

@@ -212,25 +212,27 @@ extern "C" int cvxgpu_compress_sharded(cvxgpu_shard* sh, const float* d_slab, in
     Nccl& N = nccl();
     const Shape gs = make_shape(nx, ny, nz, bx, by, bz);
     const long ncells_total = (long)nx * ny * nz;
-    CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
-    // (1) global RMS: this rank's block-row sums -> all ranks' -> the same fixed-order total everywhere
+    // (1) global RMS: this rank's block-row sums -> all ranks' -> the same fixed-order total everywhere -> header, glob_mulfac
+    const double* d_rows = nullptr;
+    int nseg = 0;
     if (!local) {
         if (nzs > 0) CU(launch_sumsq_rows(ws, d_slab, (long)nx * ny, bz, nzs, sh->world > 1 ? sh->d_rows_send : ws->d_rowsum, st));
+        d_rows = ws->d_rowsum;
         if (sh->world > 1) {
             const int nrc = N.AllGather(sh->d_rows_send, sh->d_rows_recv, (size_t)sh->seg, kNcclFloat64, sh->comm, st);
             if (nrc) return nccl_fail("ncclAllGather(row sums)", nrc);
-            CU(launch_sum_rows(sh->d_rows_recv, sh->world, sh->seg, sh->d_cnt, 0, ws->d_sumsq, st));
-        } else {
-            CU(launch_sum_rows(ws->d_rowsum, 0, 0, nullptr, nb, ws->d_sumsq, st));
+            d_rows = sh->d_rows_recv; nseg = sh->world;
         }
     }
-    CU(launch_write_header(d_header, gs, scale, local, ws->d_sumsq, ncells_total, ws->d_mulfac, st));
-    // (2) this rank's blocks -> its table slice (local offsets) and payload
-    CU(cudaMemsetAsync(sh->d_nbytes, 0, sizeof(long), st));
+    CU(launch_rms_header(d_rows, nseg, sh->seg, sh->d_cnt, nb, ws->d_sumsq, d_header, gs, scale, local, ncells_total, ws->d_mulfac, st));
+    // (2) this rank's blocks -> its table slice (local offsets) and payload; launch_encode clears *d_status and the byte count
     if (nzs > 0) {
         const Shape ss = make_shape(nx, ny, nzs, bx, by, bz);
         CU(launch_encode(ws, d_slab, ss, scale, local, ws->d_mulfac, d_offs, d_blkmulfac, d_payload, payload_capacity,
                          sh->d_nbytes, d_status, cvx_internal_exact_mode(), st));
+    } else {
+        CU(cudaMemsetAsync(d_status, 0, sizeof(int), st));
+        CU(cudaMemsetAsync(sh->d_nbytes, 0, sizeof(long), st));
     }
     // (3) payload sizes -> exclusive prefix -> global offsets
     const long nblk_slab = (long)nb * gs.nbx * gs.nby;
