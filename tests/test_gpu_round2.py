@@ -373,3 +373,32 @@ def test_large_block_wavelet_only(gpu, shape, mode):
     api.wavelet_blocks_device(d, bx, by, bz, inverse=True)
     back = d.cpu().numpy().reshape(-1)
     assert np.max(np.abs(back - src)) < 1e-5
+
+
+@pytest.mark.parametrize("nx", [96, 101, 102, 70])
+@pytest.mark.parametrize("shift", [0, 1])
+def test_ws_decoder_row_stores_any_width_and_alignment(gpu, nx, shift):
+    """k_decode32ws stores rows straight from registers (Copy_From_Block clipping, Block_Copy.cpp:136-212): odd nx, an odd
+    plane size, a clipped last column and a volume that is only 4-byte aligned must all equal the fused decoder bit for bit
+    and leave the cells around the volume untouched."""
+    import torch
+    from cvxcompress_b200 import _lib
+    api = gpu
+    L = _lib.lib()
+    ny, nz = 45, 70
+    api.set_transform("lifting")
+    vol = torch.from_numpy(synth.g2(nx, ny, nz)).cuda()
+    s, ln, _ = api.compress_device(vol, 32, 32, 32, 1e-2)
+    n = nx * ny * nz
+    outs = []
+    for ws in (1, 0):
+        L.cvx_debug_set_ws(ws)
+        buf = torch.full((n + 8,), 123.0, dtype=torch.float32, device="cuda")
+        out = buf[shift:shift + n].view(nz, ny, nx)
+        api.decompress_device(s, ln, nx, ny, nz, out=out)
+        torch.cuda.synchronize()
+        assert float(buf[:shift].sum().item()) == 123.0 * shift and torch.all(buf[shift + n:] == 123.0)
+        outs.append(out.clone())
+    L.cvx_debug_set_ws(1)
+    assert torch.equal(outs[0], outs[1])
+    assert _snr(vol, outs[0]) > 40
