@@ -69,8 +69,8 @@ def select_config(args):
 def metric_name(args, world):
     if args.config == 5:
         return "Decompress MCells/s of a reference-written stream, %dx%dx%d fp32, %d^3 blocks, %d B200" % (NX, NY, NZ, BX, world)
-    return "Compress+Decompress round-trip MCells/s, %dx%dx%d fp32, %dx%dx%d blocks, %s RMS" % (
-        NX, NY, NZ if args.scaling == "strong" else NZ * world, BX, BY, BZ, "local" if LOCAL else "global")
+    return "Compress+Decompress round-trip MCells/s, %dx%dx%d fp32, %dx%dx%d blocks, %s RMS, %s arithmetic" % (
+        NX, NY, NZ if args.scaling == "strong" else NZ * world, BX, BY, BZ, "local" if LOCAL else "global", args.transform.upper())
 
 
 def parse_args():
@@ -674,7 +674,10 @@ def run_ours(args):
             sys.exit(3)
 
     if rank == 0:
-        nker = (0 if LOCAL else 3) + 3
+        # our kernels per step: [k_sumsq_rows, k_sumsq_rows_finish] (global RMS), k_rms_header, k_encode_prep, the encoder,
+        # k_finish_length | k_shard_fixup (Compress); [k_shard_extent], the decoder (Decompress).  NCCL kernels are not counted.
+        names = ([] if LOCAL else ["k_sumsq_rows", "k_sumsq_rows_finish"]) + ["k_rms_header", "k_encode_prep", enc_name,
+                 "k_shard_fixup" if world > 1 else "k_finish_length"] + (["k_shard_extent"] if world > 1 else []) + [dec_name]
         line = {"metric": metric_name(args, world), "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling if world > 1 else "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
@@ -682,10 +685,8 @@ def run_ours(args):
                 "compress_ms": tc_ms, "decompress_ms": td_ms, "host_wall_ms_per_step": host_ms,
                 "compressed_length": length, "ratio": 4.0 * cells_total / length, "roundtrip_error": err, "snr_db": snr,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_pageable": e2e_pageable, "clocks": clocks,
-                "gpu_launches": (nker + 1 + (1 if world > 1 else 0)) * K,
-                "gpu_launches_detail": "per step: %sk_write_header, %s, %s (Compress) + %s%s (Decompress)%s" % (
-                    "" if LOCAL else "k_sumsq_rows, k_sumsq_rows_finish, k_sum_rows, ", enc_name,
-                    "k_shard_fixup + 2 ncclAllGather" if world > 1 else "k_finish_length", "k_shard_extent, " if world > 1 else "", dec_name,
+                "gpu_launches": len(names) * K,
+                "gpu_launches_detail": "per step and rank: " + ", ".join(names) + (" (+ 2 ncclAllGather)" if world > 1 else "") + (
                     "; each direction replayed from one CUDA graph" if (world > 1 and not args.no_graph) else ""),
                 "exact_mode": exact_info, "weak": weak, "strong_scaling_fixed_cost": fixed, "numa": numa}
         emit(line)
