@@ -637,8 +637,9 @@ def run_ours(args):
         fixed = {"sharded_compress_of_a_64x64x%d_volume_ms" % (BZ * world): t_fix, "same_without_cuda_graph_ms": t_fix_eager,
                  "compress_ms": tc_ms, "compress_kernels_ms": ksum, "compress_overhead_ms": tc_ms - ksum,
                  "decompress_ms": td_ms, "decompress_kernel_ms": kern[dec_name]["ms"],
+                 "exchange": "peer-memory mailboxes (CUDA IPC over NVLink)" if L.cvxgpu_shard_uses_peer_memory(sharded.NcclShard.get().handle) else "2 ncclAllGather",
                  "note": "overhead = whole sharded call minus its two hot kernels timed alone; the tiny-volume call is the floor of that overhead "
-                         "(launch gaps + 2 ncclAllGather of 8..%d bytes + the small kernels)" % (8 * max(1, -(-NZ // BZ // world)))}
+                         "(launch gaps + the exchange of 8..%d bytes per rank + the small kernels)" % (8 * max(1, -(-NZ // BZ // world)))}
         del gt
 
     # -- a short weak-scaling run beside the strong one: every rank a full volume's worth of planes --

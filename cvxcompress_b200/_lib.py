@@ -27,7 +27,7 @@ C_SYMBOLS = [
     "cvx_compress", "cvx_decompress_outofplace", "cvx_decompress_inplace", "cvx_compress_th",
     "cvx_decompress_inplace_th", "cvxgpu_validate_stream", "cvxgpu_set_safe_decode", "cvxgpu_get_safe_decode",
     "cvxgpu_workspace_release_thread_default", "cvxgpu_sumsq_rows_device", "cvxgpu_sum_rows_device",
-    "cvxgpu_shard_range", "cvxgpu_shard_unique_id", "cvxgpu_shard_create", "cvxgpu_shard_destroy",
+    "cvxgpu_shard_range", "cvxgpu_shard_unique_id", "cvxgpu_shard_create", "cvxgpu_shard_destroy", "cvxgpu_shard_uses_peer_memory",
     "cvxgpu_compress_sharded", "cvxgpu_decompress_sharded", "cvxgpu_decompress_slab_device",
 ]
 
@@ -101,6 +101,7 @@ def lib():
     L.cvxgpu_shard_unique_id.argtypes = [p]
     L.cvxgpu_shard_create.argtypes = [C.POINTER(p), p, p, i, i]
     L.cvxgpu_shard_destroy.argtypes = [p]
+    L.cvxgpu_shard_uses_peer_memory.argtypes = [p]
     L.cvxgpu_compress_sharded.argtypes = [p, p, i, i, i, i, i, i, f, i, p, p, p, p, l, p, p, p]
     L.cvxgpu_decompress_sharded.argtypes = [p, p, i, i, i, i, i, i, i, p, p, p, p, p, p]
     L.cvxgpu_decompress_slab_device.argtypes = [p, p, i, i, i, i, i, i, i, i, i, p, l, p]

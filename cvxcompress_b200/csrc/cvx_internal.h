@@ -85,6 +85,14 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
                           long payload_bytes, int exact, cudaStream_t st, const float* d_glob_mulfac = nullptr,
                           const long* d_payload_bytes = nullptr, const long* d_offs_bias = nullptr);
 cudaError_t launch_shard_fixup(const long* d_sizes, int world, int rank, long* d_bases, unsigned long long* d_offs, long n, cudaStream_t st);
+cudaError_t launch_shard_push(const void* d_src, int n, int kind, unsigned long long* const* d_peers, int world, int cap, int rank,
+                              unsigned long long* d_epoch, cudaStream_t st);
+cudaError_t launch_rms_header_mailbox(unsigned long long* d_mailbox, int world, int cap, const unsigned long long* d_epoch, const int* d_cnt,
+                                      double* d_sumsq, void* d_header, const Shape& s, float scale, int use_local, long ncells_total,
+                                      float* d_mulfac_out, int* d_status, cudaStream_t st);
+cudaError_t launch_shard_fixup_mailbox(unsigned long long* d_mailbox, int world, int cap, const unsigned long long* d_epoch, int rank,
+                                       long* d_bases, unsigned long long* d_offs, long n, int* d_status, cudaStream_t st);
+size_t shard_mailbox_bytes(int world, int cap);
 cudaError_t launch_shard_extent(const long* d_bases, int rank, long* d_out2, cudaStream_t st);
 cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, int bx, int by, int bz, int inverse,
                            int exact, cudaStream_t st);

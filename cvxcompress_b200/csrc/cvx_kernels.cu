@@ -239,6 +239,103 @@ __global__ void k_shard_extent(const long* __restrict__ bases, int rank, long* _
     if (threadIdx.x == 0 && blockIdx.x == 0) { out[0] = bases[rank + 1] - bases[rank]; out[1] = bases[rank]; }
 }
 
+// ---- peer-memory exchange of the two scalars-per-rank of a sharded Compress (instead of two ncclAllGather launches) ----
+// Every rank owns a MAILBOX in its HBM that all peers of the node can write through NVLink (CUDA IPC mapping, set up once
+// per shard).  A push writes this rank's few values into its slot of EVERY rank's mailbox and then, after a system-scope
+// fence, the call's epoch into its flag there; a consumer spins on the flags of its own mailbox (its own HBM) until all
+// ranks' epochs have arrived.  Slots and flags are double-buffered by epoch parity: a rank can be at most one call ahead
+// of the slowest reader of its previous values (it needs everybody's flags of call k before it can push call k + 1).
+// The epoch lives in device memory and is advanced by the push kernel, so a captured CUDA graph replays correctly.
+struct ShardMailbox {                       // layout parameters travel by value; the memory is one allocation per rank
+    unsigned long long* base;               // [2 parities][2 kinds] x { values[world][cap], flags[world] }
+    int world, cap;
+    __host__ __device__ size_t kind_words() const { return (size_t)world * cap + world; }
+    __device__ unsigned long long* values(int parity, int kind, int r) const { return base + (size_t)(parity * 2 + kind) * kind_words() + (size_t)r * cap; }
+    __device__ unsigned long long* flag(int parity, int kind, int r) const { return base + (size_t)(parity * 2 + kind) * kind_words() + (size_t)world * cap + r; }
+};
+__device__ __forceinline__ void st_sys_u64(unsigned long long* p, unsigned long long v) { asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// src: n 64-bit values of this rank; peers[r] = rank r's mailbox base as mapped into this process
+__global__ void __launch_bounds__(128) k_shard_push(const unsigned long long* __restrict__ src, int n, int kind, unsigned long long* const* __restrict__ peers,
+                                                    int world, int cap, int rank, unsigned long long* epoch)
+{
+    __shared__ unsigned long long s_e;
+    if (threadIdx.x == 0) s_e = *epoch + 1ull;
+    __syncthreads();
+    const unsigned long long e = s_e;
+    const int parity = (int)(e & 1ull);
+    for (int i = threadIdx.x; i < world * n; i += blockDim.x) {
+        const int r = i / n, k = i - r * n;
+        ShardMailbox mb; mb.base = peers[r]; mb.world = world; mb.cap = cap;
+        st_sys_u64(mb.values(parity, kind, rank) + k, src[k]);
+    }
+    __threadfence_system();
+    __syncthreads();
+    for (int r = threadIdx.x; r < world; r += blockDim.x) {
+        ShardMailbox mb; mb.base = peers[r]; mb.world = world; mb.cap = cap;
+        st_sys_u64(mb.flag(parity, kind, rank), e);
+    }
+    if (threadIdx.x == 0) *epoch = e;
+}
+// all ranks' values of the current epoch have arrived in MY mailbox; false after ~4 s (a peer died: report, do not hang)
+__device__ __forceinline__ bool shard_wait_all(const ShardMailbox& mb, int kind, unsigned long long e)
+{
+    __shared__ int s_bad;
+    if (threadIdx.x == 0) s_bad = 0;
+    __syncthreads();
+    const int parity = (int)(e & 1ull);
+    for (int r = threadIdx.x; r < mb.world; r += blockDim.x) {
+        const long long t0 = clock64();
+        while (ld_sys_u64(mb.flag(parity, kind, r)) != e)
+            if (clock64() - t0 > 8000000000ll) { s_bad = 1; break; }
+    }
+    __threadfence_system();
+    __syncthreads();
+    return s_bad == 0;
+}
+// the mailbox variant of k_rms_header: waits for every rank's block-row sums, adds them in row order, writes header + glob_mulfac
+__global__ void __launch_bounds__(64) k_rms_header_mailbox(ShardMailbox mb, const unsigned long long* epoch, const int* __restrict__ cnt,
+                                                           double* __restrict__ sumsq, int32_t* hdr, int nx, int ny, int nz, int bx, int by, int bz,
+                                                           float scale, int use_local, long ncells, float* mulfac_out, int* d_status)
+{
+    const unsigned long long e = *epoch;
+    const bool ok = shard_wait_all(mb, 0, e);
+    if (threadIdx.x != 0) return;
+    if (!ok) *d_status = -2;
+    double s = 0.0;
+    for (int r = 0; r < mb.world; ++r)
+        for (int i = 0; i < cnt[r]; ++i) s += __longlong_as_double((long long)ld_sys_u64(mb.values((int)(e & 1ull), 0, r) + i));
+    *sumsq = s;
+    const float m = glob_mulfac_of(sumsq, ncells, scale, use_local);
+    hdr[0] = nx; hdr[1] = ny; hdr[2] = nz; hdr[3] = bx; hdr[4] = by; hdr[5] = bz;
+    hdr[6] = __float_as_int(m);
+    hdr[7] = use_local ? 1 : 0;
+    *mulfac_out = m;
+}
+// the mailbox variant of k_shard_fixup: waits for every rank's payload size
+__global__ void __launch_bounds__(256) k_shard_fixup_mailbox(ShardMailbox mb, const unsigned long long* epoch, int rank, long* __restrict__ bases,
+                                                             unsigned long long* __restrict__ offs, long n, int* d_status)
+{
+    const unsigned long long e = *epoch;
+    const bool ok = shard_wait_all(mb, 1, e);
+    const int parity = (int)(e & 1ull);
+    long base = 0;
+    for (int r = 0; r < rank; ++r) base += (long)ld_sys_u64(mb.values(parity, 1, r));
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) offs[i] += (unsigned long long)base;
+    if (i == 0) {
+        if (!ok) *d_status = -2;
+        long acc = 0;
+        for (int r = 0; r < mb.world; ++r) { bases[r] = acc; acc += (long)ld_sys_u64(mb.values(parity, 1, r)); }
+        bases[mb.world] = acc;
+    }
+}
+
 // length = 32 + 8*nnn [+ 4*nnn] + payload + 7  (CvxCompress.cpp:421-422)
 __global__ void k_finish_length(const long* payload_bytes, long table_bytes, long* length)
 {
@@ -925,6 +1022,31 @@ cudaError_t launch_shard_fixup(const long* d_sizes, int world, int rank, long* d
     k_shard_fixup<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(d_sizes, world, rank, d_bases, d_offs, n);
     return cudaGetLastError();
 }
+cudaError_t launch_shard_push(const void* d_src, int n, int kind, unsigned long long* const* d_peers, int world, int cap, int rank,
+                              unsigned long long* d_epoch, cudaStream_t st)
+{
+    k_shard_push<<<1, 128, 0, st>>>(static_cast<const unsigned long long*>(d_src), n, kind, d_peers, world, cap, rank, d_epoch);
+    return cudaGetLastError();
+}
+cudaError_t launch_rms_header_mailbox(unsigned long long* d_mailbox, int world, int cap, const unsigned long long* d_epoch, const int* d_cnt,
+                                      double* d_sumsq, void* d_header, const Shape& s, float scale, int use_local, long ncells_total,
+                                      float* d_mulfac_out, int* d_status, cudaStream_t st)
+{
+    ShardMailbox mb; mb.base = d_mailbox; mb.world = world; mb.cap = cap;
+    k_rms_header_mailbox<<<1, 64, 0, st>>>(mb, d_epoch, d_cnt, d_sumsq, reinterpret_cast<int32_t*>(d_header), s.nx, s.ny, s.nz, s.bx, s.by, s.bz,
+                                           scale, use_local, ncells_total, d_mulfac_out, d_status);
+    return cudaGetLastError();
+}
+cudaError_t launch_shard_fixup_mailbox(unsigned long long* d_mailbox, int world, int cap, const unsigned long long* d_epoch, int rank,
+                                       long* d_bases, unsigned long long* d_offs, long n, int* d_status, cudaStream_t st)
+{
+    ShardMailbox mb; mb.base = d_mailbox; mb.world = world; mb.cap = cap;
+    const long nn = n > 0 ? n : 1;
+    k_shard_fixup_mailbox<<<(unsigned)((nn + 255) / 256), 256, 0, st>>>(mb, d_epoch, rank, d_bases, d_offs, n, d_status);
+    return cudaGetLastError();
+}
+size_t shard_mailbox_bytes(int world, int cap) { return sizeof(unsigned long long) * 4 * ((size_t)world * cap + world); }
+
 cudaError_t launch_shard_extent(const long* d_bases, int rank, long* d_out2, cudaStream_t st)
 {
     k_shard_extent<<<1, 32, 0, st>>>(d_bases, rank, d_out2);

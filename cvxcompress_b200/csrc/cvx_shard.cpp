@@ -5,7 +5,10 @@
 //   * global RMS (CvxCompress.cpp:73-117)           -> all-gather of the per-BLOCK-ROW sums of squares, added in row order
 //                                                      on every rank: glob_mulfac and the stream are identical for any G
 //   * payload offsets (CvxCompress.cpp:365-390,:302) -> all-gather of one int64 payload size per rank, exclusive prefix
-// Everything is enqueued on the caller's stream (kernels and the two ncclAllGather calls): no host synchronisation, so
+// The two scalars travel through PEER MEMORY when the ranks can map each other's HBM (one process per GPU on one NVSwitch
+// node: CUDA IPC): the producing side pushes its values into every rank's mailbox and the consuming kernel spins on its
+// own mailbox's flags (cvx_kernels.cu, ShardMailbox) -- no collective launch on the path; otherwise by two ncclAllGather.
+// Everything is enqueued on the caller's stream (kernels and, in the fallback, the two ncclAllGather calls): no host synchronisation, so
 // the sequence can be captured in a CUDA graph.  NCCL is bound at run time (dlsym on the process, then libnccl.so.2),
 // so the library has no link-time dependency on it and shares the communicator of a host application that already
 // has one.  Decompress needs no collective.
@@ -33,7 +36,7 @@ int cvx_internal_exact_mode();
 namespace {
 typedef struct ncclComm* ncclComm_t;
 struct ncclUniqueId { char internal[128]; };
-constexpr int kNcclInt64 = 4, kNcclFloat64 = 8;         // ncclDataType_t values (nccl.h)
+constexpr int kNcclUint8 = 1, kNcclInt32 = 2, kNcclInt64 = 4, kNcclFloat64 = 8;         // ncclDataType_t values (nccl.h)
 struct Nccl {
     int (*GetUniqueId)(ncclUniqueId*) = nullptr;
     int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
@@ -92,6 +95,13 @@ struct cvxgpu_shard {
     long* d_nbytes = nullptr;           // [0] this rank's payload bytes (encode output) [1],[2] extent scratch of decode
     // geometry the scratch was sized for
     int g_nz = -1, g_bz = -1;
+    // peer-memory exchange (cvx_kernels.cu: ShardMailbox): this rank's mailbox, every rank's mailbox as mapped here, epochs
+    bool p2p = false;
+    int mcap = 0;
+    unsigned long long* d_mailbox = nullptr;
+    unsigned long long** d_peers = nullptr;
+    unsigned long long* d_epoch = nullptr;      // [0] row sums, [1] payload sizes
+    std::vector<void*> opened;
 };
 
 extern "C" int cvxgpu_shard_range(int nz, int bz, int rank, int world, int* z0, int* nz_slab, int* brow0, int* nbrows)
@@ -119,6 +129,9 @@ extern "C" int cvxgpu_shard_unique_id(void* id128)
     return CVXGPU_OK;
 }
 
+// 1: the per-rank scalars of a sharded Compress travel through peer-memory mailboxes; 0: by ncclAllGather (or world == 1)
+extern "C" int cvxgpu_shard_uses_peer_memory(const cvxgpu_shard* sh) { return sh && sh->world > 1 && sh->p2p ? 1 : 0; }
+
 extern "C" int cvxgpu_shard_destroy(cvxgpu_shard* sh)
 {
     if (!sh) return CVXGPU_OK;
@@ -127,10 +140,64 @@ extern "C" int cvxgpu_shard_destroy(cvxgpu_shard* sh)
     if (sh->d_cnt) cudaFree(sh->d_cnt);
     if (sh->d_sizes) cudaFree(sh->d_sizes);
     if (sh->d_nbytes) cudaFree(sh->d_nbytes);
+    for (void* q : sh->opened) cudaIpcCloseMemHandle(q);
+    if (sh->d_mailbox) cudaFree(sh->d_mailbox);
+    if (sh->d_peers) cudaFree(sh->d_peers);
+    if (sh->d_epoch) cudaFree(sh->d_epoch);
     if (sh->ws) cvxgpu_workspace_destroy(sh->ws);
     if (sh->own_comm && sh->comm) nccl().CommDestroy(sh->comm);
     delete sh;
     return CVXGPU_OK;
+}
+
+// Map every rank's mailbox into this process (CUDA IPC over NVLink / NVSwitch peer access).  Collective over the shard's
+// communicator: all ranks use the mailboxes or none does (a rank that cannot map a peer -- several ranks in ONE process,
+// no peer access, CVX_GPU_SHARD_EXCHANGE=nccl -- votes no).  Never fails the shard: NCCL remains the fallback.
+static void shard_setup_mailboxes(cvxgpu_shard* sh)
+{
+    Nccl& N = nccl();
+    const int W = sh->world, cap = 64;
+    const char* env = getenv("CVX_GPU_SHARD_EXCHANGE");
+    int ok = !(env && !strcmp(env, "nccl"));
+    const size_t bytes = shard_mailbox_bytes(W, cap);
+    unsigned char* d_h = nullptr;                // [0, 64): my handle, [64, 64 + 64 W): everybody's, then W ints of votes
+    std::vector<unsigned char> h((size_t)64 * W);
+    std::vector<int> votes((size_t)W, 0);
+    cudaIpcMemHandle_t mine;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    memset(&mine, 0, sizeof(mine));
+    if (cudaMalloc(&sh->d_mailbox, bytes) != cudaSuccess || cudaMemset(sh->d_mailbox, 0, bytes) != cudaSuccess ||
+        cudaMalloc(&sh->d_epoch, 16) != cudaSuccess || cudaMemset(sh->d_epoch, 0, 16) != cudaSuccess ||
+        cudaMalloc(&sh->d_peers, sizeof(void*) * W) != cudaSuccess || cudaIpcGetMemHandle(&mine, sh->d_mailbox) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+    if (cudaMalloc(&d_h, 64 + 64 * (size_t)W + 8 * (size_t)W) != cudaSuccess) { cudaGetLastError(); return; }   // nothing collective has started yet
+    cudaMemcpy(d_h, &mine, 64, cudaMemcpyHostToDevice);
+    bool coll = N.AllGather(d_h, d_h + 64, 64, kNcclUint8, sh->comm, 0) == 0 && cudaStreamSynchronize(0) == cudaSuccess;
+    if (coll) cudaMemcpy(h.data(), d_h + 64, (size_t)64 * W, cudaMemcpyDeviceToHost);
+    std::vector<unsigned long long*> peers((size_t)W, nullptr);
+    if (coll && ok) {
+        for (int r = 0; r < W && ok; ++r) {
+            if (r == sh->rank) { peers[(size_t)r] = sh->d_mailbox; continue; }
+            cudaIpcMemHandle_t hr;
+            memcpy(&hr, h.data() + (size_t)64 * r, 64);
+            void* q = nullptr;
+            if (cudaIpcOpenMemHandle(&q, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+            sh->opened.push_back(q);
+            peers[(size_t)r] = static_cast<unsigned long long*>(q);
+        }
+    }
+    // the vote: one int per rank
+    int* d_v = reinterpret_cast<int*>(d_h + 64 + 64 * (size_t)W);
+    const int myvote = (coll && ok) ? 1 : 0;
+    cudaMemcpy(d_v + W, &myvote, 4, cudaMemcpyHostToDevice);
+    bool all = coll && N.AllGather(d_v + W, d_v, 1, kNcclInt32, sh->comm, 0) == 0 && cudaStreamSynchronize(0) == cudaSuccess;
+    if (all) {
+        cudaMemcpy(votes.data(), d_v, 4 * (size_t)W, cudaMemcpyDeviceToHost);
+        for (int r = 0; r < W; ++r) all = all && votes[(size_t)r] == 1;
+    }
+    if (all) all = cudaMemcpy(sh->d_peers, peers.data(), sizeof(void*) * W, cudaMemcpyHostToDevice) == cudaSuccess;
+    cudaFree(d_h);
+    sh->p2p = all;
+    sh->mcap = cap;
 }
 
 extern "C" int cvxgpu_shard_create(cvxgpu_shard** out, const void* id128, void* nccl_comm, int rank, int world)
@@ -162,6 +229,7 @@ extern "C" int cvxgpu_shard_create(cvxgpu_shard** out, const void* id128, void* 
         cvxgpu_shard_destroy(sh);
         return FAIL(CVXGPU_ERR_CUDA, "cvxgpu_shard_create: %s", cudaGetErrorString(e));
     }
+    if (world > 1) shard_setup_mailboxes(sh);           // optional: on any failure the two scalars travel by ncclAllGather
     *out = sh;
     return CVXGPU_OK;
 }
@@ -213,18 +281,26 @@ extern "C" int cvxgpu_compress_sharded(cvxgpu_shard* sh, const float* d_slab, in
     const Shape gs = make_shape(nx, ny, nz, bx, by, bz);
     const long ncells_total = (long)nx * ny * nz;
     // (1) global RMS: this rank's block-row sums -> all ranks' -> the same fixed-order total everywhere -> header, glob_mulfac
+    const bool mailbox = sh->world > 1 && sh->p2p && sh->seg <= sh->mcap;      // else the two scalars travel by ncclAllGather
     const double* d_rows = nullptr;
     int nseg = 0;
     if (!local) {
         if (nzs > 0) CU(launch_sumsq_rows(ws, d_slab, (long)nx * ny, bz, nzs, sh->world > 1 ? sh->d_rows_send : ws->d_rowsum, st));
         d_rows = ws->d_rowsum;
-        if (sh->world > 1) {
+        if (mailbox) {
+            CU(launch_shard_push(sh->d_rows_send, nb, 0, sh->d_peers, sh->world, sh->mcap, sh->rank, sh->d_epoch, st));
+        } else if (sh->world > 1) {
             const int nrc = N.AllGather(sh->d_rows_send, sh->d_rows_recv, (size_t)sh->seg, kNcclFloat64, sh->comm, st);
             if (nrc) return nccl_fail("ncclAllGather(row sums)", nrc);
             d_rows = sh->d_rows_recv; nseg = sh->world;
         }
     }
-    CU(launch_rms_header(d_rows, nseg, sh->seg, sh->d_cnt, nb, ws->d_sumsq, d_header, gs, scale, local, ncells_total, ws->d_mulfac, st));
+    if (mailbox && !local) {
+        CU(launch_rms_header_mailbox(sh->d_mailbox, sh->world, sh->mcap, sh->d_epoch, sh->d_cnt, ws->d_sumsq, d_header, gs, scale, local,
+                                     ncells_total, ws->d_mulfac, d_status, st));
+    } else {
+        CU(launch_rms_header(d_rows, nseg, sh->seg, sh->d_cnt, nb, ws->d_sumsq, d_header, gs, scale, local, ncells_total, ws->d_mulfac, st));
+    }
     // (2) this rank's blocks -> its table slice (local offsets) and payload; launch_encode clears *d_status and the byte count
     if (nzs > 0) {
         const Shape ss = make_shape(nx, ny, nzs, bx, by, bz);
@@ -236,7 +312,10 @@ extern "C" int cvxgpu_compress_sharded(cvxgpu_shard* sh, const float* d_slab, in
     }
     // (3) payload sizes -> exclusive prefix -> global offsets
     const long nblk_slab = (long)nb * gs.nbx * gs.nby;
-    if (sh->world > 1) {
+    if (mailbox) {
+        CU(launch_shard_push(sh->d_nbytes, 1, 1, sh->d_peers, sh->world, sh->mcap, sh->rank, sh->d_epoch + 1, st));
+        CU(launch_shard_fixup_mailbox(sh->d_mailbox, sh->world, sh->mcap, sh->d_epoch + 1, sh->rank, d_bases, d_offs, nblk_slab, d_status, st));
+    } else if (sh->world > 1) {
         const int nrc = N.AllGather(sh->d_nbytes, sh->d_sizes, 1, kNcclInt64, sh->comm, st);
         if (nrc) return nccl_fail("ncclAllGather(payload sizes)", nrc);
         CU(launch_shard_fixup(sh->d_sizes, sh->world, sh->rank, d_bases, d_offs, nblk_slab, st));

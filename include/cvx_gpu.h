@@ -198,9 +198,10 @@ int cvxgpu_decode_blocks_device(cvxgpu_workspace* ws, float* d_vol_slab, int nx,
  * as `nccl_comm`.  world == 1 needs neither.
  *
  * cvxgpu_compress_sharded enqueues on cuda_stream, without host synchronisation (CUDA-graph capturable
- * after one eager call):  block-row sums of squares of the slab -> ncclAllGather -> fixed-order total ->
- * header + glob_mulfac -> encode the slab's blocks -> ncclAllGather of the payload sizes -> exclusive
- * prefix, offsets made global.  Outputs, all DEVICE memory of this rank:
+ * after one eager call):  block-row sums of squares of the slab -> exchange -> fixed-order total ->
+ * header + glob_mulfac -> encode the slab's blocks -> exchange of the payload sizes -> exclusive
+ * prefix, offsets made global.  "exchange" = a store into every rank's peer-memory mailbox, or ncclAllGather
+ * (cvxgpu_shard_uses_peer_memory).  Outputs, all DEVICE memory of this rank:
  *   d_header   32 bytes, identical on every rank (CvxCompress.cpp:284-300)
  *   d_offs     this rank's slice of the offset table, nblk_slab entries, offsets relative to the GLOBAL
  *              payload start (bit 63 = raw);  d_blkmulfac  its slice of the multiplier table (local RMS)
@@ -218,6 +219,11 @@ int cvxgpu_shard_range(int nz, int bz, int rank, int world, int* z0, int* nz_sla
 int cvxgpu_shard_unique_id(void* id128);
 int cvxgpu_shard_create(cvxgpu_shard** sh, const void* id128, void* nccl_comm, int rank, int world);
 int cvxgpu_shard_destroy(cvxgpu_shard* sh);
+/* How the two per-rank scalars of cvxgpu_compress_sharded travel: 1 = through peer memory (every rank's mailbox is mapped
+ * into every process with CUDA IPC at cvxgpu_shard_create; the producing kernel stores into all mailboxes over NVLink, the
+ * consuming kernel spins on its own -- no collective launch on the path), 0 = two ncclAllGather (ranks that cannot map
+ * each other, e.g. several ranks in one process, or CVX_GPU_SHARD_EXCHANGE=nccl).  All ranks of a shard agree. */
+int cvxgpu_shard_uses_peer_memory(const cvxgpu_shard* sh);
 int cvxgpu_compress_sharded(cvxgpu_shard* sh, const float* d_slab, int nx, int ny, int nz, int bx, int by, int bz,
                             float scale, int use_local_rms, void* d_header, unsigned long long* d_offs,
                             float* d_blkmulfac, void* d_payload, long payload_capacity, long* d_bases,
