@@ -29,6 +29,7 @@ C_SYMBOLS = [
     "cvxgpu_workspace_release_thread_default", "cvxgpu_sumsq_rows_device", "cvxgpu_sum_rows_device",
     "cvxgpu_shard_range", "cvxgpu_shard_unique_id", "cvxgpu_shard_create", "cvxgpu_shard_destroy", "cvxgpu_shard_uses_peer_memory",
     "cvxgpu_compress_sharded", "cvxgpu_decompress_sharded", "cvxgpu_decompress_slab_device",
+    "cvxgpu_sumsq_rows_static_device",
 ]
 
 
@@ -96,6 +97,7 @@ def lib():
     L.cvxgpu_sumsq_device.argtypes = [p, p, l, p, p]
     L.cvxgpu_workspace_release_thread_default.argtypes = []
     L.cvxgpu_sumsq_rows_device.argtypes = [p, p, l, i, i, p, p]
+    L.cvxgpu_sumsq_rows_static_device.argtypes = [p, l, i, i, p, p]
     L.cvxgpu_sum_rows_device.argtypes = [p, i, p, p]
     L.cvxgpu_shard_range.argtypes = [i, i, i, i] + [C.POINTER(i)] * 4
     L.cvxgpu_shard_unique_id.argtypes = [p]

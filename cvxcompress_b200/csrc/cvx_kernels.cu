@@ -23,6 +23,7 @@
 #include "cvx_codec.cuh"
 #include "cvx_fused32.cuh"
 #include "cvx_internal.h"
+#include "../../include/cvx_gpu.h"
 #include <cudaTypedefs.h>
 
 namespace cvx {
@@ -1265,6 +1266,69 @@ cudaError_t launch_wavelet(cvxgpu_workspace* ws, float* d_blocks, long nblocks, 
 }
 
 }  // namespace cvx
+
+// ---- cvxgpu_sumsq_rows_static_device: the per-block-row reduction for callers that may not allocate ---------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, serving loops, harnesses that forbid it).  k_sumsq_rows needs SUMSQ_ROW_CTAS fp64
+// partials per block row as scratch; cvxgpu_sumsq_rows_device keeps them in a workspace that grows with cudaMalloc.  This
+// variant keeps them in a file-scope device array of fixed size instead: CVXGPU_STATIC_MAX_ROWS (4096) block rows x 128
+// partials x 8 bytes = 4 MiB, which every GPU that loads the library holds until the process exits.
+// In host code `g_static_rowpartial` is only a stand-in for the symbol, NOT a device address (a kernel given it would fault
+// or silently use host memory); the device address is looked up once per device, with that device current, by
+// cudaGetSymbolAddress below.  All calls on a device share the one array: two calls that overlap on the GPU (different
+// streams, no ordering between them) race on it.  Nothing in it has to start at zero -- every (row, CTA) slot a call's
+// finish kernel reads was written by that call's k_sumsq_rows, a zero where a CTA had no elements -- so no clearing pass
+// is needed, and what the previous call left behind is never read.
+int cvx_internal_fail(int code, const char* fmt, ...);          // cvx_api.cpp: records the message cvxgpu_last_error() returns
+
+static __device__ __align__(256) double g_static_rowpartial[(size_t)CVXGPU_STATIC_MAX_ROWS * cvx::SUMSQ_ROW_CTAS];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+double* g_static_rowpartial_addr[kStaticMaxDevices];          // device address of the array, per device ordinal (0 = not looked up)
+
+// the array's address on the CURRENT device; no allocation (the array is part of the loaded module)
+int static_rowpartial_address(double** out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cvx_internal_fail(CVXGPU_ERR_CUDA, "cvxgpu_sumsq_rows_static_device: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kStaticMaxDevices)
+        return cvx_internal_fail(CVXGPU_ERR_ARG, "cvxgpu_sumsq_rows_static_device: device ordinal %d outside 0..%d", dev, kStaticMaxDevices - 1);
+    double* p = __atomic_load_n(&g_static_rowpartial_addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void* sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_static_rowpartial);          // device `dev` is current: its copy of the array
+        if (e != cudaSuccess || !sym) {
+            cudaGetLastError();
+            return cvx_internal_fail(CVXGPU_ERR_CUDA, "cvxgpu_sumsq_rows_static_device: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        }
+        p = static_cast<double*>(sym);
+        __atomic_store_n(&g_static_rowpartial_addr[dev], p, __ATOMIC_RELEASE);   // racing threads store the same value
+    }
+    *out = p;
+    return CVXGPU_OK;
+}
+}  // namespace
+
+extern "C" int cvxgpu_sumsq_rows_static_device(const float* d_vol, long plane_cells, int bz, int nz, double* d_rowsums, void* cuda_stream)
+{
+    if (!d_vol || !d_rowsums || plane_cells <= 0 || bz <= 0 || nz <= 0)
+        return cvx_internal_fail(CVXGPU_ERR_ARG, "cvxgpu_sumsq_rows_static_device: bad argument");
+    const long rows = ((long)nz + bz - 1) / bz;
+    if (rows > CVXGPU_STATIC_MAX_ROWS)
+        return cvx_internal_fail(CVXGPU_ERR_CAPACITY, "cvxgpu_sumsq_rows_static_device: %ld block rows (nz = %d, bz = %d) exceed the static scratch of "
+                                 "%d rows; use cvxgpu_sumsq_rows_device", rows, nz, bz, CVXGPU_STATIC_MAX_ROWS);
+    double* d_partial = nullptr;
+    const int rc = static_rowpartial_address(&d_partial);
+    if (rc != CVXGPU_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    cvx::k_sumsq_rows<<<dim3(cvx::SUMSQ_ROW_CTAS, (unsigned)rows), cvx::SUMSQ_T, 0, st>>>(d_vol, plane_cells, bz, nz, d_partial);
+    cvx::k_sumsq_rows_finish<<<(unsigned)rows, 32, 0, st>>>(d_partial, d_rowsums);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cvx_internal_fail(CVXGPU_ERR_CUDA, "cvxgpu_sumsq_rows_static_device: launch: %s", cudaGetErrorString(e));
+    return CVXGPU_OK;
+}
 
 // developer aid (make TIMING=1): per-phase cycle totals stamped by thread 0 of every CTA; kind 0 = encode, 1 = decode
 extern "C" int cvx_debug_phases(unsigned long long* out, int kind, int reset)

@@ -163,6 +163,22 @@ int cvxgpu_sumsq_rows_device(cvxgpu_workspace* ws, const float* d_vol, long plan
                              double* d_rowsums, void* cuda_stream);
 int cvxgpu_sum_rows_device(const double* d_rowsums, int nrows, double* d_total, void* cuda_stream);
 
+/* cvxgpu_sumsq_rows_device without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernels, same summation order, bit-identical d_rowsums; the
+ * per-CTA partial sums live in a file-scope device array of the library instead of a workspace:
+ * CVXGPU_STATIC_MAX_ROWS block rows x 128 partials x 8 bytes = 4 MiB, held by every GPU that loads the
+ * library until the process exits.  The call takes no workspace and calls no cudaMalloc / cudaFree or any
+ * other allocating routine.  More than CVXGPU_STATIC_MAX_ROWS block rows ((nz + bz - 1) / bz) are refused
+ * with CVXGPU_ERR_CAPACITY (cvxgpu_last_error() says so); use cvxgpu_sumsq_rows_device then.
+ * All calls on one device share the array: calls that OVERLAP on the GPU (two streams without an ordering
+ * between them, two host threads) race on it -- order them on one stream or with events.  The array keeps
+ * the previous call's partial sums; none of them is read by the next call (every slot read was written by
+ * the same call first), so nothing needs clearing.  Asynchronous on `cuda_stream`. */
+#define CVXGPU_STATIC_MAX_ROWS 4096
+int cvxgpu_sumsq_rows_static_device(const float* d_vol, long plane_cells, int bz, int nz,
+                                    double* d_rowsums, void* cuda_stream);
+
 /* Encode the blocks of a volume (or slab) of nx*ny*nz_slab cells.  d_sumsq_total / ncells_total
  * define the global RMS (ignored when use_local_rms).  d_offs receives nblk entries (payload
  * offsets relative to d_payload, bit 63 = raw), d_blkmulfac nblk floats when use_local_rms (else
