@@ -633,12 +633,17 @@ def run_ours(args):
         t_fix = time_kernel(gt.replay, 50)
         barrier()
         t_fix_eager = time_kernel(lambda: sharded.compress_slab(tiny, 64, 64, BZ * world, BX, BY, BZ, SCALE, LOCAL, out=tss), 50)
-        ksum = sum(v["ms"] for k, v in kern.items() if not k.startswith("k_decode"))
+        # the per-kernel times above are THIS rank's (rank 0 may own fewer block rows than the slowest rank): take the max over
+        # ranks of both sums, as for the whole calls
+        km = torch.tensor([sum(v["ms"] for k, v in kern.items() if not k.startswith("k_decode")), kern[dec_name]["ms"]],
+                          dtype=torch.float64, device=dev)
+        dist.all_reduce(km, op=dist.ReduceOp.MAX)
+        ksum, kdec = float(km[0].item()), float(km[1].item())
         fixed = {"sharded_compress_of_a_64x64x%d_volume_ms" % (BZ * world): t_fix, "same_without_cuda_graph_ms": t_fix_eager,
                  "compress_ms": tc_ms, "compress_kernels_ms": ksum, "compress_overhead_ms": tc_ms - ksum,
-                 "decompress_ms": td_ms, "decompress_kernel_ms": kern[dec_name]["ms"],
+                 "decompress_ms": td_ms, "decompress_kernel_ms": kdec,
                  "exchange": "peer-memory mailboxes (CUDA IPC over NVLink)" if L.cvxgpu_shard_uses_peer_memory(sharded.NcclShard.get().handle) else "2 ncclAllGather",
-                 "note": "overhead = whole sharded call minus its two hot kernels timed alone; the tiny-volume call is the floor of that overhead "
+                 "note": "overhead = whole sharded call minus its two hot kernels timed alone (all three: max over ranks); the tiny-volume call is the floor of that overhead "
                          "(launch gaps + the exchange of 8..%d bytes per rank + the small kernels)" % (8 * max(1, -(-NZ // BZ // world)))}
         del gt
 
