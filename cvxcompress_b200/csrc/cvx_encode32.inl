@@ -137,52 +137,90 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             gather_block<F32_T>(sm, p.vol, p.g, iix * 32, (int)(q % p.nby) * 32, (int)(q / p.nby) * 32, s);
             __syncthreads();
         }
-        f32_pass_x<EXACT, true>(sm);
-        __syncwarp();                    // warp w owns the x rows and the y lines of z slices w and w + 16: no CTA barrier needed
-        CVX_PH(1);
-        f32_pass_y2<EXACT, true>(sm);
-        __syncthreads();
-        CVX_PH(2);
-        // z lines stay in registers: thread-line l = tid + 512 k is (x = lane, y = warp + 16 k)
-        typename PairOf<EXACT>::type vz[32];
-        {
-            const float* zl = f32_zline(sm, tid);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
-            fwd_line<32, EXACT>(vz);
-        }
-#define V_(k, r) ((k) ? p_hi(vz[r]) : p_lo(vz[r]))
-        // The coefficients go back to the block buffer (one conflict-free store per cell); the coder below works on
-        // row masks and gathers the few non-zero values from there, which costs far fewer integer instructions
-        // (half-rate pipe) than compacting them out of the registers row by row.
-        float mulfac = gmul;
-        if (p.use_local) {                                       // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348
-#pragma unroll
+        float mulfac;
+        bool sparse_ok;
+        if constexpr (EXACT) {
+            f32_pass_x<EXACT, true>(sm);
+            __syncwarp();                    // warp w owns the x rows and the y lines of z slices w and w + 16: no CTA barrier needed
+            CVX_PH(1);
+            f32_pass_y2<EXACT, true>(sm);
+            __syncthreads();
+            CVX_PH(2);
+            // z lines stay in registers: thread-line l = tid + 512 k is (x = lane, y = warp + 16 k)
+            typename PairOf<EXACT>::type vz[32];
+            {
+                const float* zl = f32_zline(sm, tid);
+    #pragma unroll
+                for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
+                fwd_line<32, EXACT>(vz);
+            }
+    #define V_(k, r) ((k) ? p_hi(vz[r]) : p_lo(vz[r]))
+            // The coefficients go back to the block buffer (one conflict-free store per cell); the coder below works on
+            // row masks and gathers the few non-zero values from there, which costs far fewer integer instructions
+            // (half-rate pipe) than compacting them out of the registers row by row.
+            mulfac = gmul;
+            if (p.use_local) {                                       // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348
+    #pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    float* zl = f32_zline(sm, tid + F32_T * k);
+    #pragma unroll
+                    for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = V_(k, r);
+                }
+                __syncthreads();
+                const float ss = EXACT ? cta_sumsq_exact<F32_T>(F32_B, s_red, [&](int i) { return sm[physr(i, 5)]; })
+                                       : cta_sumsq<F32_T>(sm, F32_B, s_red);
+                const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
+                mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+                if (tid == 0) p.blkmulfac[t] = mulfac;
+            }
+            // ---- which coefficients quantise to non-zero: one compare per cell, one ballot per row ----
+            sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
+            const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
+    #pragma unroll
             for (int k = 0; k < 2; ++k) {
                 float* zl = f32_zline(sm, tid + F32_T * k);
-#pragma unroll
-                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = V_(k, r);
+    #pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const float c = V_(k, r);
+                    if (!p.use_local) zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
+                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
+                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+                }
             }
+        } else {
+            // LIFTING: passes in the order z, y, x (cvx_fused32.cuh, "LIFTING encoders") -- the same arithmetic on the same
+            // threads as k_encode32ws, so that the two kernels stay bit-identical; here the rows go back to the block buffer
+            // and the rest of the block is coded as in EXACT mode
+            f32_pass_z2_fwd<EXACT>(sm);
             __syncthreads();
-            const float ss = EXACT ? cta_sumsq_exact<F32_T>(F32_B, s_red, [&](int i) { return sm[physr(i, 5)]; })
-                                   : cta_sumsq<F32_T>(sm, F32_B, s_red);
-            const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
-            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
-            if (tid == 0) p.blkmulfac[t] = mulfac;
-        }
-        // ---- which coefficients quantise to non-zero: one compare per cell, one ballot per row ----
-        const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
-        const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            float* zl = f32_zline(sm, tid + F32_T * k);
-#pragma unroll
-            for (int r = 0; r < 32; ++r) {
-                const float c = V_(k, r);
-                if (!p.use_local) zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
-                const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
-                if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
+            CVX_PH(1);
+            f32_pass_y2<EXACT, true>(sm);
+            __syncwarp();                // warp w owns the y lines and the x rows of z slices w and w + 16
+            CVX_PH(2);
+            float w[2][32];
+            {
+                float v[2][32];
+                f32_rows_load(sm, v);
+                fwd_lift_pair<32>(v[0], v[1], w[0], w[1]);
             }
+            f32_rows_store_coef(sm, w);
+            mulfac = gmul;
+            if (p.use_local) {
+                const float ss = cta_sumsq_rows<F32_T, CtaBar>(w, s_red);
+                const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
+                mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+                if (tid == 0) p.blkmulfac[t] = mulfac;
+            }
+            sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
+            const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
+            unsigned m0 = 0u, m1 = 0u;
+#pragma unroll
+            for (int x = 0; x < 32; ++x) {
+                m0 |= (!(fabsf(w[0][sub_to_reg<32, EXACT>(x)]) <= T) ? 1u : 0u) << x;
+                m1 |= (!(fabsf(w[1][sub_to_reg<32, EXACT>(x)]) <= T) ? 1u : 0u) << x;
+            }
+            s_nzm[tid] = m0;
+            s_nzm[tid + F32_T] = m1;
         }
         __syncthreads();
         CVX_PH(3);

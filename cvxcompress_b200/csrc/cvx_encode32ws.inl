@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
     int* s_base = reinterpret_cast<int*>(smem_raw + F32_OFF_BASE);
     uint2* s_lists = reinterpret_cast<uint2*>(smem_raw + E32_OFF_LIST);
     unsigned char* s_stage = smem_raw + E32_OFF_STAGE;
-    __shared__ uint64_t s_bar[4];                    // one per TMA box (8 z slices): a warp waits only for its own two
+    __shared__ uint64_t s_bar[1];                    // the block's four TMA boxes complete one barrier phase
     __shared__ int scratch[72];
     __shared__ float s_red[32];
     __shared__ unsigned int s_ticket[2];
@@ -72,12 +72,9 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
         const int iix = (int)(t % p.nbx);
         const unsigned int q = t / p.nbx;
         const int iiy = (int)(q % p.nby), iiz = (int)(q / p.nby);
+        mbar_expect_tx(&s_bar[0], F32_B * 4);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {            // boxes 0, 2 (warps 0..7: z slices w and w + 16) before boxes 1, 3 (warps 8..15)
-            const int b = ((i & 1) << 1) | (i >> 1);
-            mbar_expect_tx(&s_bar[b], F32_B);
-            tma_load_3d(sm + b * 8192, &tmap, &s_bar[b], iix * 32, iiy * 32, iiz * 32 + b * 8);
-        }
+        for (int b = 0; b < 4; ++b) tma_load_3d(sm + b * 8192, &tmap, &s_bar[0], iix * 32, iiy * 32, iiz * 32 + b * 8);
     };
     // the generic coder on the block buffer, all 768 threads (dense block / raw fallback, CvxCompress.cpp:350-360)
     auto dense_block = [&](long t, float mulfac, uint2* list) {
@@ -92,7 +89,7 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
     };
 
     if (tid == 0) {
-        for (int b = 0; b < 4; ++b) mbar_init(&s_bar[b], 1);
+        mbar_init(&s_bar[0], 1);
         const unsigned int t0 = atomicAdd(p.ticket, 1u);
         s_ticket[0] = t0;
         if (t0 < p.nblk) { fence_proxy_async(); issue_load(t0); }

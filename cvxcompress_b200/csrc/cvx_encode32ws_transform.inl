@@ -1,8 +1,8 @@
 // cvx_encode32ws_transform.inl -- body of k_encode32ws for the transform group (threads 0..511); see cvx_encode32ws.inl.
-// Same pipeline as k_encode32 up to the non-zero list; barriers are the group's named barrier.
+// Passes in the order z, y, x (cvx_fused32.cuh, "LIFTING encoders"): the x rows stay in registers, the block buffer is
+// free once every thread has loaded its two rows, and the non-zero list is emitted straight from the registers.
 {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
-    const int warp = tid >> 5;
     uint32_t parity = 0;
     int msgs = 0;                        // messages posted so far; message i uses list buffer i & 1
     CVX_PH_DECL;
@@ -11,128 +11,82 @@
         if (t >= p.nblk) break;
         unsigned int nt = 0;
         if (tid == 0) nt = atomicAdd(p.ticket, 1u);            // the next block's ticket: round trip hidden under the transform
-        mbar_wait(&s_bar[warp >> 3], parity);                  // the boxes holding z slices warp and warp + 16
-        mbar_wait(&s_bar[2 + (warp >> 3)], parity);
+        mbar_wait(&s_bar[0], parity);                          // the whole block (a z line crosses all four boxes)
         parity ^= 1u;
         CVX_PH(0);
-        f32_pass_x<EXACT, true>(sm);
-        __syncwarp();                    // warp w owns the x rows and the y lines of z slices w and w + 16
+        f32_pass_z2_fwd<EXACT>(sm, true);
+        ETBar::sync();
         CVX_PH(1);
         f32_pass_y2<EXACT, true>(sm);
-        ETBar::sync();
+        __syncwarp();                    // warp w owns the y lines and the x rows of z slices w and w + 16
         CVX_PH(2);
-        typename PairOf<EXACT>::type vz[32];                   // z lines in registers: (x = lane, y = warp + 16 k)
+        float w[2][32];                  // coefficients of rows tid and tid + 512: w[h][sub_to_reg(x)]
         {
-            if (warp >= 8) asm volatile("bar.sync 7, 512;" ::: "memory");      // second half starts its loads when the first half's are issued
-            const float* zl = f32_zline(sm, tid);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) p_set(vz[j], zl[j * 1024], zl[j * 1024 + 512]);
-            if (warp < 8) asm volatile("bar.arrive 7, 512;" ::: "memory");
-            fwd_line<32, EXACT>(vz);
+            float v[2][32];
+            f32_rows_load(sm, v);
+            ETBar::sync();               // every row is in registers: nobody reads the block buffer any more
+            if (tid == 0) {              // the next block streams in under the x math, the scan and the list emission
+                s_ticket[(it + 1) & 1] = nt;
+                if (nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
+            }
+            fwd_lift_pair<32>(v[0], v[1], w[0], w[1]);
         }
         float mulfac = gmul;
         if (p.use_local) {               // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348 (LIFTING: parallel fp32 reduction)
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                float* zl = f32_zline(sm, tid + E32_TT * k);
-#pragma unroll
-                for (int r = 0; r < 32; ++r) zl[reg_to_sub<32, EXACT>(r) * 1024] = k ? p_hi(vz[r]) : p_lo(vz[r]);
-            }
-            ETBar::sync();
-            const float ss = cta_sumsq<E32_TT, ETBar>(sm, F32_B, s_red);
+            const float ss = cta_sumsq_rows<E32_TT, ETBar>(w, s_red);
             const float rms = sqrtf(__fdiv_rn(ss, (float)F32_B));
             mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
             if (tid == 0) p.blkmulfac[t] = mulfac;
         }
         const bool sparse_ok = fabsf(mulfac) > 1e-30f && fabsf(mulfac) < 1e30f;
         const float T = sparse_ok ? nz_threshold(mulfac) : 0.0f;
-        if (!p.use_local) {              // coefficients back to the block buffer, one ballot per row
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                float* zl = f32_zline(sm, tid + E32_TT * k);
-#pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
-                    zl[reg_to_sub<32, EXACT>(r) * 1024] = c;
-                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
-                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
-                }
-            }
-        } else {                         // local RMS: the coefficients are already there
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-#pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const float c = k ? p_hi(vz[r]) : p_lo(vz[r]);
-                    const unsigned m = __ballot_sync(0xffffffffu, !(fabsf(c) <= T));
-                    if (lane == 0) s_nzm[reg_to_sub<32, EXACT>(r) * 32 + warp + 16 * k] = m;
-                }
-            }
-        }
-        ETBar::sync();
         CVX_PH(3);
-        int n = F32_LCAP + 1;
-        if (sparse_ok) {                 // rows 2*tid, 2*tid+1 -> list positions
-            const int c0 = __popc(s_nzm[2 * tid]), c1 = __popc(s_nzm[2 * tid + 1]);
-            const int base = cta_excl_sum<E32_TT, ETBar>(c0 + c1, scratch, n);
-            s_base[2 * tid] = base;
-            s_base[2 * tid + 1] = base + c0;
+        // ---- list positions: rows are raster-consecutive in tid (row tid, then row tid + 512): one scan of both counts ----
+        int n = F32_LCAP + 1, b0 = 0, b1 = 0;
+        if (sparse_ok) {
+            int c0 = 0, c1 = 0;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) { c0 += !(fabsf(w[0][r]) <= T) ? 1 : 0; c1 += !(fabsf(w[1][r]) <= T) ? 1 : 0; }
+            int tot;
+            const int ex = cta_excl_sum<E32_TT, ETBar>(c0 | (c1 << 16), scratch, tot);     // <= 16384 per half: no carry
+            const int tot0 = tot & 0xFFFF;
+            n = tot0 + (tot >> 16);
+            b0 = ex & 0xFFFF;
+            b1 = tot0 + (ex >> 16);
         }
-        if (tid == 0) s_dqn = 0;
         const int lb = msgs & 1;
         uint2* s_list = s_lists + lb * F32_LCAP;
         if (msgs >= 2) e32_wait(E32_BAR_EMPTY + lb);           // the coder has read this buffer's previous list
-        else ETBar::sync();                                    // s_base, s_dqn visible
         CVX_PH(4);
         if (n > F32_LCAP) {
+            // dense block (or a multiplier outside the sparse path's range): the generic coder wants the coefficients in the
+            // block buffer, which may already be receiving the next block -- let that load land, overwrite it with the rows
+            // from the registers, code together with the coder group, then fetch the next block again
+            ETBar::sync();                                     // s_ticket visible on the !sparse_ok way here
+            const unsigned int next_t = s_ticket[(it + 1) & 1];
+            if (next_t < p.nblk) { mbar_wait(&s_bar[0], parity); parity ^= 1u; }
+            f32_rows_store_coef(sm, w);
             if (tid == 0) { s_msg[lb].t = t; s_msg[lb].n = -1; s_msg[lb].mulfac = mulfac; }
-            e32_arrive(E32_BAR_FULL + lb);
+            e32_arrive(E32_BAR_FULL + lb);                     // orders every thread's rows before the coder group's reads
+            ETBar::sync();                                     // ... and before this group's
             dense_block(t, mulfac, s_list);                    // together with the coder group; ends with a CTA barrier
-            if (tid == 0) {
-                s_ticket[(it + 1) & 1] = nt;
-                if (nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
-            }
+            if (tid == 0 && next_t < p.nblk) { fence_proxy_async(); issue_load(next_t); }
             ++msgs;
-            ETBar::sync();
             continue;
         }
-        // ---- (index, value) list in raster order: rows with up to 4 non-zeros by their thread, denser rows by whole warps ----
+        // ---- (index, value) list in raster order, straight from the registers: 64 predicated stores per thread ----
+        {
+            uint32_t lp0 = smem_u32(s_list + b0), lp1 = smem_u32(s_list + b1);
+            const unsigned i0 = (unsigned)tid * 32u, i1 = i0 + (unsigned)E32_TT * 32u;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int row = tid + E32_TT * h;
-            unsigned m = s_nzm[row];
-            if (__popc(m) > 4) {
-                s_dq[atomicAdd(&s_dqn, 1)] = (unsigned short)row;
-            } else {
-                const float* rp = sm + row * 32;
-                const int sw = (row & 7) << 2;
-                int at = s_base[row];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    if (m) {
-                        const int x = __ffs(m) - 1;
-                        m &= m - 1;
-                        s_list[at++] = make_uint2((unsigned)(row * 32 + x), __float_as_uint(rp[x ^ sw]));
-                    }
-                }
+            for (int x = 0; x < 32; ++x) {
+                f32_emit_nz(lp0, w[0][sub_to_reg<32, EXACT>(x)], T, i0 | (unsigned)x);
+                f32_emit_nz(lp1, w[1][sub_to_reg<32, EXACT>(x)], T, i1 | (unsigned)x);
             }
         }
-        ETBar::sync();
-        for (int i = warp; i < s_dqn; i += E32_TT / 32) {
-            const int rr = s_dq[i];
-            const unsigned mm = s_nzm[rr];
-            if ((mm >> lane) & 1u)
-                s_list[s_base[rr] + __popc(mm & lt)] = make_uint2((unsigned)(rr * 32 + lane), __float_as_uint(sm[rr * 32 + (lane ^ ((rr & 7) << 2))]));
-        }
-        ETBar::sync();                   // list complete; nobody reads the block buffer any more
-        if (tid == 0) {
-            s_msg[lb].t = t; s_msg[lb].n = n; s_msg[lb].mulfac = mulfac;
-            s_ticket[(it + 1) & 1] = nt;
-            if (nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
-        }
-        e32_arrive(E32_BAR_FULL + lb);
+        if (tid == 0) { s_msg[lb].t = t; s_msg[lb].n = n; s_msg[lb].mulfac = mulfac; }
+        e32_arrive(E32_BAR_FULL + lb);   // every thread's entries precede its own arrival: no group barrier needed
         ++msgs;
-        ETBar::sync();                   // s_ticket visible
         CVX_PH(5);
     }
     // no more blocks: tell the coder, then absorb its last EMPTY arrival so that no barrier is left half-way

@@ -260,6 +260,89 @@ __device__ __forceinline__ float* f32_zline(float* sm, int l)
 }
 
 
+// ---- LIFTING encoders: passes in the order z, y, x, the x rows staying in registers ------------------------------------
+// The three 1-D transforms commute up to rounding, and LIFTING promises a tolerance, not the reference's bits (EXACT keeps
+// the reference's x, y, z order).  With x LAST a thread ends up holding two complete raster rows of coefficients: it counts
+// and emits their non-zeros straight from registers (no write-back of the 96 % zeros, no ballots, no gather of the values
+// out of the block buffer), and the block buffer is dead as soon as every thread has LOADED its rows, so the TMA load of
+// the next block is issued before the x math and hides under it, the scan and the list emission.
+
+// z lines in place, two per thread in packed registers: lines (x = lane, y = warp) and (x, y = warp + 16), 512 floats apart
+// with the same swizzle.  `skew` as in f32_pass_x.
+template <bool EXACT>
+__device__ __forceinline__ void f32_pass_z2_fwd(float* sm, const bool skew = false)
+{
+    float* zl = f32_zline(sm, threadIdx.x);
+    typename PairOf<EXACT>::type v[32];
+    if (skew && (threadIdx.x & 256)) asm volatile("bar.sync 7, 512;" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 32; ++j) p_set(v[j], zl[j * 1024], zl[j * 1024 + 512]);
+    if (skew && !(threadIdx.x & 256)) asm volatile("bar.arrive 7, 512;" ::: "memory");
+    fwd_line<32, EXACT>(v);
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+        const int s = reg_to_sub<32, EXACT>(r);
+        zl[s * 1024] = p_lo(v[r]);
+        zl[s * 1024 + 512] = p_hi(v[r]);
+    }
+}
+
+// the thread's two x rows (rows tid and tid + 512), natural order, into registers
+__device__ __forceinline__ void f32_rows_load(const float* sm, float (&v)[2][32])
+{
+    const float4* row0 = reinterpret_cast<const float4*>(sm + threadIdx.x * 32);
+    const int k = threadIdx.x & 7;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const float4* row = row0 + h * ((F32_T * 32) / 4);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const float4 q = row[c ^ k];
+            v[h][4 * c] = q.x; v[h][4 * c + 1] = q.y; v[h][4 * c + 2] = q.z; v[h][4 * c + 3] = q.w;
+        }
+    }
+}
+// ... and back: w[h][sub_to_reg(x)] = coefficient x of row tid + 512 h (what fwd_lift_pair leaves)
+__device__ __forceinline__ void f32_rows_store_coef(float* sm, const float (&w)[2][32])
+{
+    float4* row0 = reinterpret_cast<float4*>(sm + threadIdx.x * 32);
+    const int k = threadIdx.x & 7;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float4* row = row0 + h * ((F32_T * 32) / 4);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            row[c ^ k] = make_float4(w[h][sub_to_reg<32, false>(4 * c)], w[h][sub_to_reg<32, false>(4 * c + 1)],
+                                     w[h][sub_to_reg<32, false>(4 * c + 2)], w[h][sub_to_reg<32, false>(4 * c + 3)]);
+    }
+}
+// sum of squares of the block's coefficients from the rows in registers (local RMS, LIFTING): every thread its 64 values
+// in register order, warps by shuffle, warp sums in warp order -- the same in every kernel that uses it
+template <int T, class Bar>
+__device__ __forceinline__ float cta_sumsq_rows(const float (&w)[2][32], float* s_red)
+{
+    float a = 0.f;
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int r = 0; r < 32; ++r) a = __fmaf_rn(w[h][r], w[h][r], a);
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+    if ((threadIdx.x & 31) == 0) s_red[(threadIdx.x & (T - 1)) >> 5] = a;
+    Bar::sync();
+    float t = 0.f;
+    for (int i = 0; i < T / 32; ++i) t += s_red[i];
+    Bar::sync();
+    return t;
+}
+// appends (idx, c) at shared address lp when c quantises to non-zero, i.e. !(|c| <= T): predicated, no branch
+__device__ __forceinline__ void f32_emit_nz(uint32_t& lp, float c, float T, unsigned idx)
+{
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .f32 a;\n\tabs.f32 a, %1;\n\tsetp.gtu.f32 p, a, %2;\n\t"
+                 "@p st.shared.v2.b32 [%0], {%3, %4};\n\t@p add.u32 %0, %0, 8;\n\t}"
+                 : "+r"(lp) : "f"(c), "f"(T), "r"(idx), "r"(__float_as_uint(c)) : "memory");
+}
+
 // ---- sparse coder pieces ---------------------------------------------------------------------------
 // largest T >= 0 with |fl(m * T)| < 1, so that  quantise(fl(m * v)) != 0  <=>  !(|v| <= T)
 // (truncation gives 0 exactly when |f| < 1; NaN and out-of-range give 0x80000000, Run_Length_Encode_Slow.cpp:204).
