@@ -48,25 +48,36 @@ __device__ __forceinline__ int w32_spec_entry(const uint64_t* w64, int c, int en
     return (c == 0) ? entry : d;
 }
 
-// list entries (values the reference decoder stores, zeros of runs excluded) of the tokens starting in a chunk
-__device__ __forceinline__ int w32_count_entries(uint32_t mask, uint64_t A, uint64_t N)
+// walk of one chunk with BOTH counts in one pass: n += values, ne += list entries (values the reference decoder stores,
+// zeros of runs excluded) of the tokens that start in the chunk -- the byte, operand and token-start work is shared
+// (a separate entry-count pass over the masks cost 12 % more parser instructions: decode 2.277 -> 2.249 ms)
+__device__ __forceinline__ uint32_t w32_walk_count(uint64_t A, uint64_t N, int& d, int& n, int& ne)
 {
-    int n = 0;
+    uint32_t mask = 0;
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
-        const bool st = ((mask >> p) & 1u) != 0;
-        const int c = (int)(int8_t)((uint32_t)(A >> (8 * p)) & 0xFFu);
+        const uint32_t b = (uint32_t)(A >> (8 * p)) & 0xFFu;
+        const int L = token_len(b);
+        const bool st = (d == 0);
+        mask |= (st ? 1u : 0u) << p;
         const uint32_t op = chunk8_operand(A, N, p);
-        const bool lit = (uint32_t)(c + 124) <= 248u;
-        int q = c;
-        q = (c == VLESC2) ? (int)(int16_t)(op & 0xFFFFu) : q;
-        q = (c == VLESC3) ? ((int)(op << 8) >> 8) : q;
-        int e = ((lit || c == VLESC2 || c == VLESC3) && q != 0) ? 1 : 0;
-        e = (c == VLESC4) ? 1 : e;
-        e = (c == VLESC2_8x || c == VLESC3_8x) ? 8 : e;
-        n += st ? e : 0;
+        const bool is8 = (b == 0x7Eu || b == 0x82u);                  // VLESC3_8x, VLESC2_8x
+        int c = 1;
+        c = (b == 0x7Fu) ? (int)(op & 0xFFu) : c;                     // RLESC1
+        c = (b == 0x7Du) ? (int)(op & 0xFFFFFFu) : c;                 // RLESC3
+        c = is8 ? 8 : c;
+        // entries: a literal / VLESC2 / VLESC3 whose value is not zero, a VLESC4, eight for an 8-value token, none for runs
+        int e = (b != 0u && (b - 0x7Du) > 6u) ? 1 : 0;                // literal other than 0 (0x7D..0x83 are the escape codes)
+        e = (b == 0x83u) ? ((op & 0xFFFFu) != 0u ? 1 : 0) : e;        // VLESC2
+        e = (b == 0x81u) ? ((op & 0xFFFFFFu) != 0u ? 1 : 0) : e;      // VLESC3
+        e = (b == 0x80u) ? 1 : e;                                     // VLESC4
+        e = is8 ? 8 : e;
+        n += st ? c : 0;
+        ne += st ? e : 0;
+        d = st ? L : d;
+        d -= 1;
     }
-    return n;
+    return mask;
 }
 
 // VLESC4 and the 8-value tokens, out of line: writes 1 or 8 entries at `out`
@@ -123,12 +134,12 @@ __device__ __forceinline__ int w32_parse_to_list(const D32Src& b, const unsigned
     const int c0 = min(nch, ptid * K), c1 = min(nch, c0 + K);
     const bool active = c0 < c1;
     int ent = active ? w32_spec_entry(w64, c0, entry) : 0;
-    int ext = 0, cntv = 0;
+    int ext = 0, cntv = 0, cnte = 0;
     auto walk_range = [&](int d) {
-        cntv = 0;
+        cntv = 0; cnte = 0;
         for (int c = c0; c < c1; ++c) {
             int n = 0;
-            const uint32_t m = chunk8_walk<true>(w64[c], w64[c + 1], d, n);
+            const uint32_t m = w32_walk_count(w64[c], w64[c + 1], d, n, cnte);
             s_mask[c] = (unsigned char)m;
             cntv = min(cntv + min(n, 1 << 20), 1 << 20);
         }
@@ -143,8 +154,6 @@ __device__ __forceinline__ int w32_parse_to_list(const D32Src& b, const unsigned
         if (!PBar::sync_or(bad ? 1 : 0)) break;
         if (bad) { ent = want; walk_range(ent); }
     }
-    int cnte = 0;
-    for (int c = c0; c < c1; ++c) cnte += w32_count_entries((uint32_t)s_mask[c], w64[c], w64[c + 1]);
     unsigned long long total;
     const unsigned long long ex = d32_excl_sum64<W32_PT, PBar>((unsigned long long)(unsigned)cntv | ((unsigned long long)(unsigned)cnte << 32), scratch64, total);
     const long totv = (long)(total & 0xFFFFFFFFull), tote = (long)(total >> 32);
@@ -153,6 +162,18 @@ __device__ __forceinline__ int w32_parse_to_list(const D32Src& b, const unsigned
     uint2* out = list + (int)(ex >> 32);
     for (int c = c0; c < c1; ++c) vi = w32_expand_list((uint32_t)s_mask[c], w64[c], w64[c + 1], 8 * c, vi, b.scalefac, win, out);
     return (int)tote;
+}
+
+
+// The block buffer must be all zero before a block's list is scattered into it.  Instead of 64 zero stores per transform
+// thread (1024 shared-memory store wavefronts per block on the critical group) one thread asks the bulk-copy engine to
+// overwrite the buffer from a 128 KiB page of zeros that stays in L2: asynchronous, no LSU slots, hidden under the z math
+// and the row stores.
+__device__ __align__(128) unsigned char g_zero_page[F32_B * 4];
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
@@ -173,6 +194,9 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint8_t* hi = p.payload + p.payload_bytes;
     if ((long)blockIdx.x >= p.nblk) return;
+    __shared__ uint64_t s_zbar;                                     // completion of the block buffer's bulk zero fill
+    if (tid == 0) mbar_init(&s_zbar, 1);
+    __syncthreads();
 
     if (tid >= W32_TT) {
         // ------------------------------ parser group ------------------------------
@@ -240,9 +264,11 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
     unsigned char* win2 = s_win + 2 * D32_WIN;                      // window of the in-line path
     CVX_PH_DECL;
     int tb = 0;                                                     // list buffer of the block at hand
+    uint32_t zparity = 0;
     for (long t = blockIdx.x; t < p.nblk; t += gridDim.x, tb ^= 1) {
         CVX_PH(5);
         w32_wait(W32_BAR_FULL + tb);                                // also orders every thread's zeroing before the scatter
+        if (t != (long)blockIdx.x) { mbar_wait(&s_zbar, zparity); zparity ^= 1u; }      // the bulk zero fill issued in the previous iteration has landed
         CVX_PH(0);
         const int n = s_ctl[tb];
         const uint2* s_list = s_lists + tb * W32_LCAP;
@@ -295,8 +321,20 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
                 p_set(v[r], e[0], e[512]);
             }
             if (warp < 8) asm volatile("bar.arrive 7, 512;" ::: "memory");
+            // every thread's z lines are in registers -> the buffer may be overwritten: warps 0..14 arrive (no wait), warp 15
+            // (last to start its loads, see the skew) waits and one of its lanes issues the zero fill when there is a next block
+            if (t + gridDim.x < p.nblk) {
+                if (warp != 15) asm volatile("bar.arrive 8, 512;" ::: "memory");
+                else {
+                    asm volatile("bar.sync 8, 512;" ::: "memory");
+                    if (lane == 0) {
+                        fence_proxy_async();
+                        mbar_expect_tx(&s_zbar, F32_B * 4);
 #pragma unroll
-            for (int r = 0; r < 32; ++r) { zl[r * 1024] = 0.f; zl[r * 1024 + 512] = 0.f; }
+                        for (int b = 0; b < 4; ++b) bulk_g2s(sm + b * 8192, g_zero_page + b * 32768, 32768, &s_zbar);
+                    }
+                }
+            }
         }
         const int iix = (int)(t % p.nbx);
         const long q = t / p.nbx;
@@ -311,7 +349,9 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
             if (gx < p.g.nx && gy < p.g.ny) {
                 float* dp = p.vol + ((long)gz0 * p.g.ny + gy) * p.g.nx + gx;
                 if (nzl == 32 && plane < (1L << 30)) {
-                    // plane j of the block: one 32 x 32 -> 64 bit multiply-add per row store (IMAD.WIDE) instead of a carried 64-bit add
+                    // plane j of the block at byte offset pb * j: ptxas turns this into shift / add chains, about three
+                    // instructions per row store.  (Forcing one IMAD.WIDE with an immediate j per store through PTX was
+                    // measured SLOWER: decode 2.28 -> 2.55 ms.)
                     const unsigned pb = (unsigned)plane * 4u;
 #pragma unroll
                     for (int j = 0; j < 32; ++j)

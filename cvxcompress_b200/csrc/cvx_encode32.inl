@@ -119,6 +119,8 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
     };
 
     uint32_t parity = 0;
+    float row_fa = 1.0f, row_fb = 1.0f;      // LIFTING: y / z scalings of the thread's two x rows
+    if constexpr (!EXACT) f32_row_factors(row_fa, row_fb);
     CVX_PH_DECL;
     for (int it = 0;; ++it) {
         const long t = s_ticket[it & 1];
@@ -201,7 +203,7 @@ __global__ void __launch_bounds__(F32_T, 1) k_encode32(const __grid_constant__ C
             {
                 float v[2][32];
                 f32_rows_load(sm, v);
-                fwd_lift_pair<32>(v[0], v[1], w[0], w[1]);
+                fwd_lift_pair_rs<32>(v[0], v[1], w[0], w[1], row_fa, row_fb);
             }
             f32_rows_store_coef(sm, w);
             mulfac = gmul;

@@ -4,6 +4,8 @@
 {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
     uint32_t parity = 0;
+    float row_fa, row_fb;                // y / z scalings of the thread's two x rows
+    f32_row_factors(row_fa, row_fb);
     int msgs = 0;                        // messages posted so far; message i uses list buffer i & 1
     CVX_PH_DECL;
     for (int it = 0;; ++it) {
@@ -29,7 +31,7 @@
                 s_ticket[(it + 1) & 1] = nt;
                 if (nt < p.nblk) { fence_proxy_async(); issue_load(nt); }
             }
-            fwd_lift_pair<32>(v[0], v[1], w[0], w[1]);
+            fwd_lift_pair_rs<32>(v[0], v[1], w[0], w[1], row_fa, row_fb);
         }
         float mulfac = gmul;
         if (p.use_local) {               // Compute_Local_RMS, CvxCompress.cpp:119-142, :343-348 (LIFTING: parallel fp32 reduction)

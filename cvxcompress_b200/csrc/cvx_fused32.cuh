@@ -75,6 +75,24 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
         : "memory");
 }
 
+// ---- y and z lines of the 32^3 kernels.  The LIFTING encoders (passes z, y, x) run the bare lifting steps here: the
+//      lines' scalings ride on the x rows' multiply (cvx_wavelet.cuh, "the scalings of all three axes in ONE multiply").
+//      Everything else -- EXACT, and the LIFTING decoders -- is the plain line transform. ----
+template <bool EXACT, bool FWD, class V>
+__device__ __forceinline__ void f32_line_yz(V* v)
+{
+    if constexpr (EXACT) { if (FWD) fwd_line<32, EXACT>(v); else inv_line<32, EXACT>(v); }
+    else { if (FWD) fwd_lift_levels<32, 1>(v); else inv_line<32, EXACT>(v); }
+}
+// factors of the thread's two x rows (row tid: y = lane, z = warp; row tid + 512: z = warp + 16) of a 512-thread group
+__device__ __forceinline__ void f32_row_factors(float& fa, float& fb)
+{
+    const int y = threadIdx.x & 31, z = (threadIdx.x >> 5) & 15;
+    const float sy = lift_scale_of_sub<32, true>(y);
+    fa = __fmul_rn(sy, lift_scale_of_sub<32, true>(z));
+    fb = __fmul_rn(sy, lift_scale_of_sub<32, true>(z + 16));
+}
+
 // ---- line passes on the swizzled 32^3 block: addresses reduced to a base register + immediates ----
 // element (x, y, z) lives at float index  z*1024 + y*32 + (x ^ ((y & 7) << 2))
 
@@ -171,7 +189,7 @@ __device__ __forceinline__ void f32_pass_y2(float* sm)
     if (FWD) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) p_set(v[j], a[j & 7][j * 32], a[j & 7][j * 32 + 16384]);
-        fwd_line<32, EXACT>(v);
+        f32_line_yz<EXACT, true>(v);
 #pragma unroll
         for (int r = 0; r < 32; ++r) {
             const int s = reg_to_sub<32, EXACT>(r);
@@ -184,7 +202,7 @@ __device__ __forceinline__ void f32_pass_y2(float* sm)
             const int s = reg_to_sub<32, EXACT>(r);
             p_set(v[r], a[s & 7][s * 32], a[s & 7][s * 32 + 16384]);
         }
-        inv_line<32, EXACT>(v);
+        f32_line_yz<EXACT, false>(v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             a[j & 7][j * 32] = p_lo(v[j]);
@@ -278,7 +296,7 @@ __device__ __forceinline__ void f32_pass_z2_fwd(float* sm, const bool skew = fal
 #pragma unroll
     for (int j = 0; j < 32; ++j) p_set(v[j], zl[j * 1024], zl[j * 1024 + 512]);
     if (skew && !(threadIdx.x & 256)) asm volatile("bar.arrive 7, 512;" ::: "memory");
-    fwd_line<32, EXACT>(v);
+    f32_line_yz<EXACT, true>(v);
 #pragma unroll
     for (int r = 0; r < 32; ++r) {
         const int s = reg_to_sub<32, EXACT>(r);
