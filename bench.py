@@ -552,6 +552,9 @@ def run_ours(args):
     if is32:
         # LIFTING dispatches the warp-specialised kernels, EXACT the fused ones (cvx_kernels.cu launch_encode / launch_decode)
         enc_name, dec_name = ("k_encode32ws", "k_decode32ws") if args.transform == "lifting" else ("k_encode32", "k_decode32")
+    elif max(BX, BY, BZ) <= 64 and 8192 <= BX * BY * BZ <= 32768:
+        # config 4's 16 x 16 x 64 and its siblings: sparse list coder / windowed parser (cvx_encode_sparse.inl, cvx_decode_win.inl)
+        enc_name, dec_name = "k_encode_sparse", "k_decode_win"
     else:
         enc_name, dec_name = "k_encode_fused", "k_decode_fused"
     klist = [] if LOCAL else [("k_sumsq_rows", k_sumsq, 4 * cells_rank)]

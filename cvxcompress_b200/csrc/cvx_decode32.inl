@@ -29,9 +29,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // stage the window [cbase, cbase + D32_WIN) (cbase 16-byte aligned); bytes at or beyond `hi` read as zero
-__device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi, int nthreads)
+__device__ __forceinline__ void d32_issue_window(unsigned char* win, const uint8_t* cbase, const uint8_t* hi, int nthreads, int win_bytes = D32_WIN)
 {
-    for (int g = threadIdx.x; g < D32_WIN / 16; g += nthreads) {
+    for (int g = threadIdx.x; g < win_bytes / 16; g += nthreads) {
         const uint8_t* a = cbase + 16 * g;
         long left = hi - a;
         int n = left >= 16 ? 16 : (left > 0 ? (int)left : 0);
@@ -88,7 +88,8 @@ __device__ __forceinline__ D32Raw d32_locate_issue(const DecParams& p, long t)
     if (t + 1 < p.nblk) asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(r.o1) : "l"(p.offs + t + 1));
     return r;
 }
-__device__ __forceinline__ D32Src d32_locate_finish(const DecParams& p, long t, const D32Raw& w)
+// maxch: 8-byte chunks of a window (two per thread of the parsing group; D32_CH for the 512-thread kernels)
+__device__ __forceinline__ D32Src d32_locate_finish(const DecParams& p, long t, const D32Raw& w, int maxch = D32_CH)
 {
     D32Src r;
     unsigned long long o = w.o;
@@ -102,14 +103,15 @@ __device__ __forceinline__ D32Src d32_locate_finish(const DecParams& p, long t, 
     // table says: that is the same one (k_decode32) or two (k_decode32ws parser) chunks per thread a typical ~3 KiB
     // payload takes anyway, and it serves a block of any order; a payload that turns out longer continues window by window.
     const long h = nxt - (long)o;
-    r.hint = (h > D32_MINWIN && h <= D32_CH * 8 - 16) ? h : D32_MINWIN;
+    const long minwin = D32_MINWIN < maxch * 8 - 16 ? D32_MINWIN : maxch * 8 - 16;
+    r.hint = (h > minwin && h <= maxch * 8 - 16) ? h : minwin;
     const float mulfac = p.use_local ? p.blkmulfac[t] : p.glob_mulfac;
     r.scalefac = __fdiv_rn(1.0f, mulfac);                        // Run_Length_Encode_Slow.cpp:392
     return r;
 }
-__device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t)
+__device__ __forceinline__ D32Src d32_locate(const DecParams& p, long t, int maxch = D32_CH)
 {
-    return d32_locate_finish(p, t, d32_locate_issue(p, t));
+    return d32_locate_finish(p, t, d32_locate_issue(p, t), maxch);
 }
 
 // per-thread result of walking its two chunks of a window
@@ -119,9 +121,9 @@ struct D32Walk {
     int ent[2], ext[2], cnt[2];
 };
 
-__device__ __forceinline__ int d32_nchunks(int entry, long hint)
+__device__ __forceinline__ int d32_nchunks(int entry, long hint, int maxch = D32_CH)
 {
-    int nch = D32_CH;
+    int nch = maxch;
     if (hint > 0) {
         long want = (entry + hint + 7) >> 3;
         want += want & 1;                 // even: the next window base stays 16-byte aligned
@@ -165,9 +167,10 @@ __device__ __forceinline__ void d32_walk(const unsigned char* win, int entry, in
 }
 
 // parse the block whose first window is staged in `win` and already walked (`w`); writes coefficients through put(i, v)
+// num: cells of the block; maxch: chunks of a window (<= 2 T)
 template <int T, class Bar, class PutV>
 __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, unsigned char* win, int* s_ext,
-                                          unsigned long long* scratch64, D32Walk& w, PutV put)
+                                          unsigned long long* scratch64, D32Walk& w, PutV put, const int num = F32_B, const int maxch = D32_CH)
 {
     const int tid = threadIdx.x;
     const uint8_t* cbase = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(b.src) & ~(uintptr_t)15);
@@ -176,10 +179,10 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
     int produced = 0;
     auto getb = [win](int k) -> uint32_t { return (uint32_t)win[k]; };
     for (bool first = true;; first = false) {
-        const int nch = d32_nchunks(entry, hint);
+        const int nch = d32_nchunks(entry, hint, maxch);
         if (!first) {                     // rare: payload longer than one window, or a wrong hint
             Bar::sync();
-            d32_issue_window(win, cbase, hi, T);
+            d32_issue_window(win, cbase, hi, T, maxch * 8 + 32);
             cp_async_wait_all();
             Bar::sync();
             d32_walk<T>(win, entry, nch, w);
@@ -213,11 +216,11 @@ __device__ __forceinline__ void d32_parse(const uint8_t* hi, const D32Src& b, un
         const long tot0 = (long)(total & 0xFFFFFFFFull), tot1 = (long)(total >> 32);
         long vi0 = (long)produced + (long)(ex & 0xFFFFFFFFull);
         long vi1 = (long)produced + tot0 + (long)(ex >> 32);
-        if (w.mask[0] && vi0 < F32_B) chunk8_expand(w.mask[0], w.A[0], w.N[0], 8 * tid, (int)vi0, F32_B, b.scalefac, getb, put);
-        if (w.mask[1] && vi1 < F32_B) chunk8_expand(w.mask[1], w.A[1], w.N[1], 8 * (tid + T), (int)vi1, F32_B, b.scalefac, getb, put);
+        if (w.mask[0] && vi0 < num) chunk8_expand(w.mask[0], w.A[0], w.N[0], 8 * tid, (int)vi0, num, b.scalefac, getb, put);
+        if (w.mask[1] && vi1 < num) chunk8_expand(w.mask[1], w.A[1], w.N[1], 8 * (tid + T), (int)vi1, num, b.scalefac, getb, put);
         long np = (long)produced + tot0 + tot1;
         produced = np > (1 << 30) ? (1 << 30) : (int)np;
-        if (produced >= F32_B) break;
+        if (produced >= num) break;
         cbase += 8 * nch;
         hint = 0;
         if (cbase >= hi + 64) break;      // truncated stream: stop instead of spinning

@@ -26,7 +26,7 @@ __device__ __forceinline__ unsigned long long wide_lookback(const EncParams& p, 
             const long idx = j - gtid;
             unsigned long long s = CVX_ST_PFX;                      // before ticket 0: prefix 0
             if (idx >= 0) {
-                do { s = ld_acquire_u64(&p.status[idx]); } while ((s >> 62) == 0);
+                while (((s = ld_acquire_u64(&p.status[idx])) >> 62) == 0) __nanosleep(64);      // not published yet: poll gently, the SM's other warps have work
             }
             const unsigned pfx = __ballot_sync(0xffffffffu, (s >> 62) == 2);
             const int first = pfx ? __ffs(pfx) - 1 : 32;            // nearest predecessor in this warp holding a prefix

@@ -682,6 +682,7 @@ __global__ void __launch_bounds__(T, MINB) k_encode_fused(const EncParams p)
 
 #include "cvx_encode32.inl"
 #include "cvx_encode32ws.inl"
+#include "cvx_encode_sparse.inl"
 
 // ------------------------------------------------------------------------------------------
 // Fused decode
@@ -773,6 +774,7 @@ __global__ void __launch_bounds__(T, MINB) k_decode_fused(const DecParams pin)
 
 #include "cvx_decode32.inl"
 #include "cvx_decode32ws.inl"
+#include "cvx_decode_win.inl"
 
 // forward / inverse transform of dense blocks: block k is the z-range [k*bz, (k+1)*bz) of a
 // bx * by * (bz*nblocks) volume
@@ -1142,6 +1144,15 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
         kern<<<(unsigned)grid, F32_T, F32_SMEM, st>>>(tmap, p, use_tma);
         return cudaGetLastError();
     }
+    if (es_ok(s.bx, s.by, s.bz) && !getenv("CVX_GPU_NO_SPARSE")) {
+        // 8192 .. 32768 cells (config 4's 16 x 16 x 64): the generic line passes + the sparse list coder (cvx_encode_sparse.inl)
+        const size_t smem = es_smem_bytes(p.s.B, p.nseg);
+#define CVX_CALL_ENC(MAXN, EX, T, MINB) \
+    e = launch_persistent(k_encode_sparse<MAXN, EX, T, MINB>, T, smem, s.nblk, ws->sm_count, st, p)
+        CVX_DISPATCH_FUSED(CVX_CALL_ENC);
+#undef CVX_CALL_ENC
+        return e;
+    }
     if (fused_ok(s.bx, s.by, s.bz)) {
         const size_t smem = (size_t)p.s.B * 4 + sizeof(int4) * (size_t)p.nseg;
 #define CVX_CALL_ENC(MAXN, EX, T, MINB) \
@@ -1201,6 +1212,17 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
         if (e != cudaSuccess) return e;
         kern<<<(unsigned)grid, threads, D32_SMEM, st>>>(p);
         return cudaGetLastError();
+    }
+    if (es_ok(s.bx, s.by, s.bz) && !getenv("CVX_GPU_NO_SPARSE")) {
+        // 8192 .. 32768 cells (config 4's 16 x 16 x 64): the generic line passes + k_decode32's windowed parser (cvx_decode_win.inl)
+#define CVX_CALL_DEC(MAXN, EX, T, MINB)                                                   \
+    do {                                                                                  \
+        const size_t smem = (size_t)p.s.B * 4 + 2 * (size_t)(2 * T * 8 + 32) + (size_t)(2 * T) * 4; \
+        e = launch_persistent(k_decode_win<MAXN, EX, T, MINB>, T, smem, s.nblk, ws->sm_count, st, p); \
+    } while (0)
+        CVX_DISPATCH_FUSED(CVX_CALL_DEC);
+#undef CVX_CALL_DEC
+        return e;
     }
     if (fused_ok(s.bx, s.by, s.bz)) {
 #define CVX_CALL_DEC(MAXN, EX, T, MINB)                                                   \

@@ -402,3 +402,48 @@ def test_ws_decoder_row_stores_any_width_and_alignment(gpu, nx, shift):
     L.cvx_debug_set_ws(1)
     assert torch.equal(outs[0], outs[1])
     assert _snr(vol, outs[0]) > 40
+
+
+# ---- the sparse-coder / windowed-parser kernels of the 8192 .. 32768-cell shapes (k_encode_sparse, k_decode_win) ----------
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("shape", [(16, 16, 64), (64, 16, 16), (32, 32, 16), (64, 64, 8), (32, 16, 16), (64, 32, 16)],
+                         ids=lambda s: "%dx%dx%d" % s)
+@pytest.mark.parametrize("local", [False, True], ids=["global", "local"])
+def test_mid_size_shapes_sparse_dense_raw_and_foreign_order(gpu, shape, local):
+    """BASELINE config 4's block shape and its siblings, many blocks per CTA (ragged volume: partial blocks on every side):
+    EXACT streams byte-identical to the oracle and reconstructions bit-identical -- on smooth data (sparse list coder), on
+    data + noise at a small scale (list overflow -> dense coder, long payloads -> several parser windows, raw blocks), and,
+    where the reference build travelled, on the reference's multi-threaded (permuted block order) stream; LIFTING within the
+    quality tolerance of EXACT."""
+    import torch
+    api = gpu
+    bx, by, bz = shape
+    nx, ny, nz = 200, 150, 132
+    rng = np.random.default_rng(7)
+    smooth = synth.g2(nx, ny, nz)
+    noisy = (smooth + rng.standard_normal(smooth.shape).astype(np.float32) * np.float32(0.3)).astype(np.float32)
+    for vol, scale in ((smooth, 1e-2), (noisy, 1e-3), (noisy, 1e-7)):
+        d = torch.from_numpy(vol).cuda()
+        want, _ = ol.oracle_compress(vol, bx, by, bz, scale, local)
+        s, ln, _ = api.compress_device(d, bx, by, bz, scale, local)
+        got = s[:ln].cpu().numpy()
+        assert _streams_equal(got, want), (shape, local, scale)
+        rec = api.decompress_device(s, ln, nx, ny, nz).cpu().numpy()
+        ref = ol.oracle_decompress(want, nx, ny, nz)
+        assert np.array_equal(rec.view(np.uint32), ref.view(np.uint32)), (shape, local, scale)
+        if ol.have_ref():
+            s_ref, _ = ol.ref_compress(vol, bx, by, bz, scale, local, threads=4)
+            rec2 = api.decompress_device(torch.from_numpy(np.ascontiguousarray(s_ref)).cuda(), len(s_ref), nx, ny, nz).cpu().numpy()
+            assert np.array_equal(rec2.view(np.uint32), ref.view(np.uint32)), (shape, local, scale, "foreign order")
+    # LIFTING: same quality, decodable by the oracle
+    d = torch.from_numpy(smooth).cuda()
+    s0, ln0, _ = api.compress_device(d, bx, by, bz, 1e-2, local)
+    _, snr0 = synth.quality(smooth, api.decompress_device(s0, ln0, nx, ny, nz).cpu().numpy())
+    api.set_transform("lifting")
+    s1, ln1, _ = api.compress_device(d, bx, by, bz, 1e-2, local)
+    rec1 = api.decompress_device(s1, ln1, nx, ny, nz).cpu().numpy()
+    ref1 = ol.oracle_decompress(s1[:ln1].cpu().numpy(), nx, ny, nz)
+    api.set_transform("exact")
+    _, snr1 = synth.quality(smooth, rec1)
+    assert abs(snr1 - snr0) < 0.1 and abs(ln1 - ln0) <= 0.005 * ln0
+    assert float(np.max(np.abs(rec1 - ref1))) <= 2e-5 * float(np.max(np.abs(smooth)))
