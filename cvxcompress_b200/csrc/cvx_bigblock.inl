@@ -230,6 +230,201 @@ __global__ void __launch_bounds__(N <= 64 ? 128 : 64) k_big_strided(const BigPar
     }
 }
 
+// ---- long lines (128, 256 samples), LIFTING: four lanes of a warp share a line ----------------------------------------
+// One thread per 128- or 256-long line means a serial walk through shared memory, ~32 shared-memory accesses per sample and
+// 64 threads per CTA: 0.05 / 0.035 of the 16 N roofline at 128^3 / 256^3.  Here each of four lanes holds a contiguous
+// quarter of the line in registers (C = N / 4 samples at positions g * C + i).  A level with stride S < C works inside
+// the quarters; the ONE neighbour value a lifting step needs across a quarter boundary comes by shuffle (the lanes of a
+// line are D apart).  The last two levels (one sample per quarter) are gathered by shuffles and computed by every lane.
+// Same operations in the same order as fwd_lift_mem / inv_lift_mem: bit-identical results.
+#define LCS(j) v[S * 2 * (j)]
+#define LCD(j) v[S * (2 * (j) + 1)]
+template <int C, int S>
+__device__ __forceinline__ void lc_fwd_levels(float* v, const bool first, const bool last, const int D)
+{
+    constexpr int m = C / S / 2;
+    float nb = __shfl_down_sync(0xffffffffu, LCS(0), D);           // s_0 of the next quarter (line end: mirror, s_m -> s_(m-1))
+    nb = last ? LCS(m - 1) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCD(j) = CVX_FMA(CVX_LA, CVX_ADD(LCS(j), j + 1 < m ? LCS(j + 1) : nb), LCD(j));
+    nb = __shfl_up_sync(0xffffffffu, LCD(m - 1), D);               // last d of the previous quarter (line start: d_(-1) -> d_0)
+    nb = first ? LCD(0) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCS(j) = CVX_FMA(CVX_LB, CVX_ADD(j > 0 ? LCD(j - 1) : nb, LCD(j)), LCS(j));
+    nb = __shfl_down_sync(0xffffffffu, LCS(0), D);
+    nb = last ? LCS(m - 1) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCD(j) = CVX_FMA(CVX_LG, CVX_ADD(LCS(j), j + 1 < m ? LCS(j + 1) : nb), LCD(j));
+    nb = __shfl_up_sync(0xffffffffu, LCD(m - 1), D);
+    nb = first ? LCD(0) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCS(j) = CVX_FMA(CVX_LD, CVX_ADD(j > 0 ? LCD(j - 1) : nb, LCD(j)), LCS(j));
+    if constexpr (2 * S < C) lc_fwd_levels<C, 2 * S>(v, first, last, D);
+}
+template <int C, int S>
+__device__ __forceinline__ void lc_inv_levels(float* v, const bool first, const bool last, const int D)
+{
+    if constexpr (2 * S < C) lc_inv_levels<C, 2 * S>(v, first, last, D);       // coarse levels first
+    constexpr int m = C / S / 2;
+    float nb = __shfl_up_sync(0xffffffffu, LCD(m - 1), D);
+    nb = first ? LCD(0) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCS(j) = CVX_FMA(-CVX_LD, CVX_ADD(j > 0 ? LCD(j - 1) : nb, LCD(j)), LCS(j));
+    nb = __shfl_down_sync(0xffffffffu, LCS(0), D);
+    nb = last ? LCS(m - 1) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCD(j) = CVX_FMA(-CVX_LG, CVX_ADD(LCS(j), j + 1 < m ? LCS(j + 1) : nb), LCD(j));
+    nb = __shfl_up_sync(0xffffffffu, LCD(m - 1), D);
+    nb = first ? LCD(0) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCS(j) = CVX_FMA(-CVX_LB, CVX_ADD(j > 0 ? LCD(j - 1) : nb, LCD(j)), LCS(j));
+    nb = __shfl_down_sync(0xffffffffu, LCS(0), D);
+    nb = last ? LCS(m - 1) : nb;
+#pragma unroll
+    for (int j = 0; j < m; ++j) LCD(j) = CVX_FMA(-CVX_LA, CVX_ADD(LCS(j), j + 1 < m ? LCS(j + 1) : nb), LCD(j));
+}
+#undef LCS
+#undef LCD
+// the whole line transform on the quarter v[0..C) of lane-quarter g (lane0 = lane of quarter 0 of this line)
+template <int N, bool FWD>
+__device__ __forceinline__ void lc_line(float* v, const int g, const int lane0, const int D)
+{
+    constexpr int C = N / 4, LOGN = N == 128 ? 7 : 8;
+    const bool first = g == 0, last = g == 3;
+    if constexpr (FWD) {
+        lc_fwd_levels<C, 1>(v, first, last, D);
+        float q[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] = __shfl_sync(0xffffffffu, v[0], lane0 + k * D);
+        fwd_lift_levels<4, 1>(q);
+        v[0] = g == 0 ? q[0] : g == 1 ? q[1] : g == 2 ? q[2] : q[3];
+        v[0] = CVX_MUL(lift_scale_rt(g * C, LOGN, true), v[0]);
+#pragma unroll
+        for (int i = 1; i < C; ++i) v[i] = CVX_MUL(lift_scale_rt(i, LOGN, true), v[i]);     // ctz(g * C + i) == ctz(i)
+    } else {
+        v[0] = CVX_MUL(lift_scale_rt(g * C, LOGN, false), v[0]);
+#pragma unroll
+        for (int i = 1; i < C; ++i) v[i] = CVX_MUL(lift_scale_rt(i, LOGN, false), v[i]);
+        float q[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] = __shfl_sync(0xffffffffu, v[0], lane0 + k * D);
+        inv_lift_levels<4, 1>(q);
+        v[0] = g == 0 ? q[0] : g == 1 ? q[1] : g == 2 ? q[2] : q[3];
+        lc_inv_levels<C, 1>(v, first, last, D);
+    }
+}
+
+// x pass, long lines, LIFTING: 32 rows per tile, four adjacent lanes per row.  Shared-memory row = four quarters of C + 1
+// floats (pitch 4 C + 4 = 4 mod 32): the 32 lanes of a warp reading element i of their quarters hit 32 different banks.
+template <int N, bool FWD>
+__global__ void __launch_bounds__(128) k_big_x_coop(const BigParams p)
+{
+    constexpr int C = N / 4, RT = 32, PITCH = 4 * (C + 1);
+    extern __shared__ __align__(16) float s_tile[];   // [RT][PITCH]
+    const long rows_per_blk = p.s.B / N;
+    const long nrows = (long)p.nb * rows_per_blk;
+    const long ntiles = (nrows + RT - 1) / RT;
+    const int tid = threadIdx.x;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long r0 = tile * RT;
+        const int nrow = (int)min((long)RT, nrows - r0);
+        for (int i = tid; i < nrow * N; i += 128) {
+            const int r = i / N, c = i - r * N;
+            const long row = r0 + r;
+            float x;
+            if (p.vol_in) {
+                const long k = row / rows_per_blk, rr = row - k * rows_per_blk;
+                int x0, y0, z0;
+                big_block_origin(p, k, x0, y0, z0);
+                const int gy = y0 + (int)(rr & (p.s.by - 1)), gz = z0 + (int)(rr >> p.s.lby), gx = x0 + c;
+                x = (gx < p.g.nx && gy < p.g.ny && gz < p.g.nz) ? __ldg(p.vol_in + ((long)gz * p.g.ny + gy) * p.g.nx + gx) : 0.f;
+            } else {
+                x = p.scratch[row * N + c];
+            }
+            const int at = FWD ? c : lift_pos_rt(c, N);           // the inverse wants sub-band c at its interleaved position
+            s_tile[r * PITCH + (at / C) * (C + 1) + (at % C)] = x;
+        }
+        __syncthreads();
+        {
+            const int g = tid & 3;
+            float* q = s_tile + (tid >> 2) * PITCH + g * (C + 1);
+            float v[C];
+#pragma unroll
+            for (int i = 0; i < C; ++i) v[i] = q[i];
+            lc_line<N, FWD>(v, g, (tid & 31) & ~3, 1);
+#pragma unroll
+            for (int i = 0; i < C; ++i) q[i] = v[i];
+        }
+        __syncthreads();
+        for (int i = tid; i < nrow * N; i += 128) {
+            const int r = i / N, c = i - r * N;
+            const int at = FWD ? lift_pos_rt(c, N) : c;           // the forward leaves sub-band c at an interleaved position
+            p.scratch[(r0 + r) * N + c] = s_tile[r * PITCH + (at / C) * (C + 1) + (at % C)];
+        }
+        __syncthreads();
+    }
+}
+
+// y / z pass, long lines, LIFTING: a warp owns 8 consecutive lines (consecutive x: 32-byte segments per row), lane = g * 8 + line
+template <int N, bool FWD>
+__global__ void __launch_bounds__(128) k_big_strided_coop(const BigParams p, const int axis)
+{
+    constexpr int C = N / 4;
+    const long lines_per_blk = p.s.B / N;
+    const long total = (long)p.nb * lines_per_blk;
+    const long stride = axis == 1 ? p.s.bx : (long)p.s.bx * p.s.by;
+    const bool scatter = p.vol_out != nullptr;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 3, l8 = lane & 7;
+    for (long l0 = (long)blockIdx.x * 32; l0 < total; l0 += (long)gridDim.x * 32) {
+        const long l = l0 + warp * 8 + l8;
+        const bool act = l < total;
+        const long k = act ? l / lines_per_blk : 0, ll = act ? l - k * lines_per_blk : 0;
+        float* blk = p.scratch + k * p.s.B;
+        const long base = axis == 1 ? (ll >> p.s.lbx) * ((long)p.s.bx * p.s.by) + (ll & (p.s.bx - 1)) : ll;
+        float* vdst = nullptr;
+        int nclip = 0;
+        long vstride = 0;
+        if (scatter && act) {
+            int x0, y0, z0;
+            big_block_origin(p, k, x0, y0, z0);
+            const int gx = x0 + (int)(ll & (p.s.bx - 1)), go = (int)(ll >> p.s.lbx);
+            if (axis == 2) {
+                if (gx < p.g.nx && y0 + go < p.g.ny) {
+                    vdst = p.vol_out + ((long)z0 * p.g.ny + y0 + go) * p.g.nx + gx;
+                    nclip = min(N, p.g.nz - z0);
+                    vstride = (long)p.g.nx * p.g.ny;
+                }
+            } else if (gx < p.g.nx && z0 + go < p.g.nz) {
+                vdst = p.vol_out + ((long)(z0 + go) * p.g.ny + y0) * p.g.nx + gx;
+                nclip = min(N, p.g.ny - y0);
+                vstride = p.g.nx;
+            }
+        }
+        float v[C];
+#pragma unroll
+        for (int i = 0; i < C; ++i) {
+            const int pos = g * C + i;
+            v[i] = act ? blk[base + (long)(FWD ? pos : lift_pos_to_idx(pos, N)) * stride] : 0.f;
+        }
+        lc_line<N, FWD>(v, g, l8, 8);
+        if (act) {
+            if (scatter) {
+                if (vdst) {
+#pragma unroll
+                    for (int i = 0; i < C; ++i) if (g * C + i < nclip) vdst[(long)(g * C + i) * vstride] = v[i];
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < C; ++i) {
+                    const int pos = g * C + i;
+                    blk[base + (long)(FWD ? lift_pos_to_idx(pos, N) : pos) * stride] = v[i];
+                }
+            }
+        }
+    }
+}
+
 template <bool EXACT, bool FWD>
 static cudaError_t launch_big_axis(const BigParams& p, int axis, int sm_count, cudaStream_t st)
 {
@@ -257,6 +452,30 @@ static cudaError_t launch_big_axis(const BigParams& p, int axis, int sm_count, c
         if (grid > (long)sm_count * 32) grid = (long)sm_count * 32;                                                \
         k_big_strided<NN, EXACT, FWD><<<(unsigned)grid, T, smem, st>>>(p, axis);                                   \
         break;                                                                                                     \
+    }
+    if (!EXACT && n >= 128 && !getenv("CVX_GPU_NO_COOP")) {
+        // long lines, LIFTING: four lanes per line, quarters in registers (k_big_x_coop / k_big_strided_coop)
+        long grid = (lines + 31) / 32;
+        const long cap = (long)sm_count * (axis == 0 ? 16 : 32);
+        if (grid > cap) grid = cap;
+        cudaError_t e = cudaSuccess;
+        if (axis == 0) {
+            const size_t smem = (size_t)32 * 4 * (n / 4 + 1) * 4;
+            if (n == 128) {
+                e = cudaFuncSetAttribute(k_big_x_coop<128, FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                k_big_x_coop<128, FWD><<<(unsigned)grid, 128, smem, st>>>(p);
+            } else {
+                e = cudaFuncSetAttribute(k_big_x_coop<256, FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                k_big_x_coop<256, FWD><<<(unsigned)grid, 128, smem, st>>>(p);
+            }
+        } else if (n == 128) {
+            k_big_strided_coop<128, FWD><<<(unsigned)grid, 128, 0, st>>>(p, axis);
+        } else {
+            k_big_strided_coop<256, FWD><<<(unsigned)grid, 128, 0, st>>>(p, axis);
+        }
+        return cudaGetLastError();
     }
     if (axis == 0) {
         switch (n) { CVX_BIG_X(8) CVX_BIG_X(16) CVX_BIG_X(32) CVX_BIG_X(64) CVX_BIG_X(128) CVX_BIG_X(256) default: return cudaErrorInvalidValue; }
