@@ -13,14 +13,18 @@ namespace cvx {
 // group g (block-wide group index).  Returns the block's encoded length in bytes.
 // scratch: >= 66 ints.
 // ------------------------------------------------------------------------------------------
+// `measured`: s_seg already holds every segment's { has, lead, trail, inner } (written by another kernel: the large-block
+// path measures the segments of a whole batch grid-wide); s_seg may then be global memory.
 template <int T, class Get8>
-__device__ __forceinline__ int cta_rle_plan(int nseg, int gps, float mulfac, Get8 get8, int4* s_seg, int* scratch)
+__device__ __forceinline__ int cta_rle_plan(int nseg, int gps, float mulfac, Get8 get8, int4* s_seg, int* scratch, const bool measured = false)
 {
     const int tid = threadIdx.x;
-    for (int seg = tid; seg < nseg; seg += T) {
-        const int g0 = seg * gps;
-        SegSum s = seg_measure(gps, mulfac, [&](int g, float* c) { get8(g0 + g, c); });
-        s_seg[seg] = make_int4(s.has, s.lead, s.trail, s.inner);
+    if (!measured) {
+        for (int seg = tid; seg < nseg; seg += T) {
+            const int g0 = seg * gps;
+            SegSum s = seg_measure(gps, mulfac, [&](int g, float* c) { get8(g0 + g, c); });
+            s_seg[seg] = make_int4(s.has, s.lead, s.trail, s.inner);
+        }
     }
     __syncthreads();
     const int V = gps * 8;

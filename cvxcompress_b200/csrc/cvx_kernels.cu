@@ -830,6 +830,112 @@ __global__ void __launch_bounds__(STAGE_T, 1) k_stage_encode(const EncParams p, 
     }
 }
 
+// ---- large blocks, coder on many CTAs -------------------------------------------------------------------------------
+// k_stage_encode gives a block to ONE CTA: at 256^3 (64 MiB of coefficients) every thread walks 32768 cells twice, and a
+// volume has fewer such blocks than the GPU has SMs -- 315 ms per Compress of the config-3 volume, no faster than the
+// reference's host threads.  The segment coder is already a parallel decomposition (cvx_codec.cuh: measure every segment,
+// scan the zero-run carries and the byte counts, emit every segment at its offset); here its three steps are three
+// launches over the whole BATCH with segments of STG_V cells:
+//   k_stage_mulfac   (local RMS only) one CTA per block: the reference's summation order -> block multiplier
+//   k_stage_measure  one thread per segment, grid-wide: { has, lead, trail, inner } into global memory
+//   k_stage_plan     one CTA per block: carry + byte-count scans over the block's segments (cta_rle_plan on the global array),
+//                    raw decision (CvxCompress.cpp:350), payload offset by the decoupled look-back, table entry
+//   k_stage_emit     one thread per segment, grid-wide: tokens (or raw coefficients) at the segment's final address
+// Byte-identical to k_stage_encode: the segmentation does not show in the stream.
+constexpr int STG_V = 256;                       // cells per segment (32 groups of eight)
+struct StageCoder {
+    const float* scratch;            // nb dense blocks of coefficients
+    int4* seg;                       // nb * (B / STG_V) segment records
+    float* mulfac;                   // nb block multipliers
+    unsigned long long* blkoff;      // nb payload offsets (bit 63: raw, all ones: does not fit)
+    long blk_first;
+    int nb;
+};
+__device__ __forceinline__ void stage_get8(const float* coef, long g, float* c)
+{
+    const float4* q = reinterpret_cast<const float4*>(coef + g * 8);
+    const float4 a = q[0], b = q[1];
+    c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+}
+__global__ void __launch_bounds__(STAGE_T, 1) k_stage_mulfac(const EncParams p, const StageCoder sc)
+{
+    __shared__ float s_red[32];
+    const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
+    for (int k = blockIdx.x; k < sc.nb; k += gridDim.x) {
+        float mulfac = gmul;
+        if (p.use_local) {
+            // large-block path: always the reference's summation order (the multiplier travels in the stream)
+            const float* coef = sc.scratch + (long)k * p.s.B;
+            const float ss = cta_sumsq_exact<STAGE_T>(p.s.B, s_red, [&](int i) { return __ldg(coef + i); });
+            const float rms = sqrtf(__fdiv_rn(ss, (float)p.s.B));
+            mulfac = rms != 0.0f ? __fdiv_rn(1.0f, __fmul_rn(rms, p.scale)) : 1.0f;
+            if (threadIdx.x == 0) p.blkmulfac[sc.blk_first + k] = mulfac;
+        }
+        if (threadIdx.x == 0) sc.mulfac[k] = mulfac;
+    }
+}
+__global__ void __launch_bounds__(256) k_stage_measure(const EncParams p, const StageCoder sc)
+{
+    const long S = p.s.B / STG_V, total = (long)sc.nb * S;
+    for (long sid = (long)blockIdx.x * 256 + threadIdx.x; sid < total; sid += (long)gridDim.x * 256) {
+        const long k = sid / S, seg = sid - k * S;
+        const float* coef = sc.scratch + k * p.s.B + seg * STG_V;
+        const SegSum m = seg_measure(STG_V / 8, sc.mulfac[k], [&](int g, float* c) { stage_get8(coef, g, c); });
+        sc.seg[sid] = make_int4(m.has, m.lead, m.trail, m.inner);
+    }
+}
+__global__ void __launch_bounds__(STAGE_T, 1) k_stage_plan(const EncParams p, const StageCoder sc)
+{
+    __shared__ int scratch_i[72];
+    const int S = (int)(p.s.B / STG_V);
+    // blocks of the batch are taken in order: CTA b plans block blk_first + b (+ k * gridDim.x)
+    for (int k = blockIdx.x; k < sc.nb; k += gridDim.x) {
+        const long t = sc.blk_first + k;
+        const int len = cta_rle_plan<STAGE_T>(S, STG_V / 8, 0.f, [](int, float*) {}, sc.seg + (long)k * S, scratch_i, true);
+        const bool raw = (long)len > 4L * p.s.B;              // CvxCompress.cpp:350
+        const unsigned long long nbytes = raw ? (unsigned long long)(4L * p.s.B) : (unsigned long long)len;
+        if (warp_id() == 0) {
+            const unsigned long long excl = lookback_exclusive(p.status, t, nbytes);
+            if (lane_id() == 0) {
+                p.offs[t] = excl | (raw ? 0x8000000000000000ull : 0ull);      // :382-384
+                if (t == p.nblk - 1) *p.payload_bytes = (long)(excl + nbytes);
+                const bool fits = (long)(excl + nbytes) <= p.cap;
+                if (!fits) *p.err = -3;
+                sc.blkoff[k] = fits ? (excl | (raw ? 0x8000000000000000ull : 0ull)) : ~0ull;
+            }
+        }
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(256) k_stage_emit(const EncParams p, const StageCoder sc)
+{
+    const long S = p.s.B / STG_V, total = (long)sc.nb * S;
+    for (long sid = (long)blockIdx.x * 256 + threadIdx.x; sid < total; sid += (long)gridDim.x * 256) {
+        const long k = sid / S, seg = sid - k * S;
+        const unsigned long long bo = sc.blkoff[k];
+        if (bo == ~0ull) continue;                            // does not fit: nothing is written, the call reports CAPACITY
+        const float* coef = sc.scratch + k * p.s.B + seg * STG_V;
+        uint8_t* dst = p.payload + (bo & 0x7FFFFFFFFFFFFFFFull);
+        if (bo >> 63) {                                       // raw block: B fp32 coefficients in raster order (:355-360)
+            uint8_t* d = dst + 4 * seg * STG_V;
+            if ((reinterpret_cast<uintptr_t>(d) & 3) == 0) {
+                for (int i = 0; i < STG_V; ++i) reinterpret_cast<float*>(d)[i] = coef[i];
+            } else {
+                for (int i = 0; i < STG_V; ++i) {
+                    const uint32_t u = __float_as_uint(coef[i]);
+                    d[4 * i] = (uint8_t)u; d[4 * i + 1] = (uint8_t)(u >> 8); d[4 * i + 2] = (uint8_t)(u >> 16); d[4 * i + 3] = (uint8_t)(u >> 24);
+                }
+            }
+            continue;
+        }
+        const int4 q = sc.seg[sid];                           // { zeros carried in, byte offset inside the block payload, has, - }
+        const bool last = seg == S - 1;
+        if (!q.z && !last) continue;
+        seg_emit(STG_V / 8, sc.mulfac[k], q.x, q.y, last, [&](int g, float* c) { stage_get8(coef, g, c); },
+                 [&](int pos, uint8_t b) { dst[pos] = b; });
+    }
+}
+
 __global__ void __launch_bounds__(STAGE_T, 1) k_stage_decode(const DecParams pin, float* scratch, long blk_first, int nb)
 {
     const DecParams p = dec_resolve(pin);
@@ -1110,6 +1216,16 @@ static void rle_segments(const BlkShape& b, int& nseg, int& gps)
     gps = V / 8;
 }
 
+// blocks per batch of the large-block path: two blocks per SM (the parser still takes one CTA per block), between 256 MiB and
+// 2 GiB of scratch -- at 256^3 (64 MiB per block) a 256 MiB batch is four blocks, i.e. four busy SMs per launch
+static long stage_batch_blocks(size_t blk_bytes, int sm_count)
+{
+    size_t bytes = blk_bytes * (size_t)(2 * sm_count);
+    if (bytes < (256ull << 20)) bytes = 256ull << 20;
+    if (bytes > (2048ull << 20)) bytes = 2048ull << 20;
+    return (long)(bytes / blk_bytes);
+}
+
 cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape& s, float scale, int use_local,
                           const float* d_glob_mulfac, unsigned long long* d_offs, float* d_blkmulfac,
                           void* d_payload, long cap, long* d_payload_bytes, int* d_err, int exact, cudaStream_t st)
@@ -1163,11 +1279,16 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
     }
     // staged: batches of blocks through global scratch
     const size_t blk_bytes = (size_t)p.s.B * 4;
-    long per_batch = (long)((256ull << 20) / blk_bytes);
+    long per_batch = stage_batch_blocks(blk_bytes, ws->sm_count);
     if (per_batch < 1) per_batch = 1;
     if (per_batch > s.nblk) per_batch = s.nblk;
-    e = ws_reserve_scratch(ws, blk_bytes * (size_t)per_batch);
+    // scratch: the batch's dense blocks, then the coder's segment records and per-block multipliers / offsets
+    const size_t blocks_bytes = blk_bytes * (size_t)per_batch;
+    const size_t seg_bytes = (blocks_bytes / 4 / STG_V) * sizeof(int4);
+    const size_t per_blk_bytes = ((size_t)per_batch * 16 + 255) & ~(size_t)255;
+    e = ws_reserve_scratch(ws, blocks_bytes + seg_bytes + per_blk_bytes);
     if (e != cudaSuccess) return e;
+    const bool one_cta_coder = getenv("CVX_GPU_STAGE_ONE_CTA") != nullptr;          // developer switch: the coder these kernels replace
     for (long b0 = 0; b0 < s.nblk; b0 += per_batch) {
         const int nb = (int)((s.nblk - b0) < per_batch ? (s.nblk - b0) : per_batch);
         BigParams bp;
@@ -1176,7 +1297,24 @@ cudaError_t launch_encode(cvxgpu_workspace* ws, const float* d_vol, const Shape&
         e = launch_big_transform(bp, true, exact != 0, ws->sm_count, st);         // gather fused into the x pass
         if (e != cudaSuccess) return e;
         const int ge = nb < ws->sm_count ? nb : ws->sm_count;
-        k_stage_encode<<<ge, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
+        if (one_cta_coder) {
+            k_stage_encode<<<ge, STAGE_T, 0, st>>>(p, ws->d_scratch, b0, nb);
+        } else {
+            StageCoder sc;
+            unsigned char* base = reinterpret_cast<unsigned char*>(ws->d_scratch);
+            sc.scratch = ws->d_scratch;
+            sc.seg = reinterpret_cast<int4*>(base + blocks_bytes);
+            sc.blkoff = reinterpret_cast<unsigned long long*>(base + blocks_bytes + seg_bytes);
+            sc.mulfac = reinterpret_cast<float*>(base + blocks_bytes + seg_bytes + (size_t)per_batch * 8);
+            sc.blk_first = b0; sc.nb = nb;
+            const long nsegs = (long)nb * (p.s.B / STG_V);
+            long gs = (nsegs + 255) / 256;
+            if (gs > (long)ws->sm_count * 16) gs = (long)ws->sm_count * 16;
+            k_stage_mulfac<<<ge, STAGE_T, 0, st>>>(p, sc);
+            k_stage_measure<<<(unsigned)gs, 256, 0, st>>>(p, sc);
+            k_stage_plan<<<ge, STAGE_T, 0, st>>>(p, sc);
+            k_stage_emit<<<(unsigned)gs, 256, 0, st>>>(p, sc);
+        }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -1235,7 +1373,7 @@ cudaError_t launch_decode(cvxgpu_workspace* ws, float* d_vol, const Shape& s, fl
         return e;
     }
     const size_t blk_bytes = (size_t)p.s.B * 4;
-    long per_batch = (long)((256ull << 20) / blk_bytes);
+    long per_batch = stage_batch_blocks(blk_bytes, ws->sm_count);
     if (per_batch < 1) per_batch = 1;
     if (per_batch > s.nblk) per_batch = s.nblk;
     e = ws_reserve_scratch(ws, blk_bytes * (size_t)per_batch);

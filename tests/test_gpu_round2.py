@@ -345,6 +345,18 @@ def test_large_blocks_full_pipeline(gpu, shape):
     ref3 = ol.oracle_decompress(s3[:ln3].cpu().numpy(), nx, ny, nz)
     rec3 = api.decompress_device(s3, ln3, nx, ny, nz).cpu().numpy()
     assert np.max(np.abs(rec3 - ref3)) <= 2e-5 * np.max(np.abs(vol))
+    # the many-CTA coder of the large-block path (k_stage_measure / plan / emit): EXACT streams byte-identical with local RMS,
+    # and on noise at a tiny scale (wide tokens, raw blocks), for both RMS kinds
+    api.set_transform("exact")
+    rng = np.random.default_rng(11)
+    noisy = (vol + rng.standard_normal(vol.shape).astype(np.float32) * np.float32(0.3)).astype(np.float32)
+    dn = torch.from_numpy(noisy).cuda()
+    for v, dv, scale, local in ((vol, d, 1e-2, True), (noisy, dn, 1e-3, False), (noisy, dn, 1e-7, False), (noisy, dn, 1e-7, True)):
+        w, _ = ol.oracle_compress(v, bx, by, bz, scale, local)
+        s4, ln4, _ = api.compress_device(dv, bx, by, bz, scale, local)
+        assert _streams_equal(s4[:ln4].cpu().numpy(), w), (shape, scale, local)
+        rec4 = api.decompress_device(s4, ln4, nx, ny, nz).cpu().numpy()
+        assert np.array_equal(rec4.view(np.uint32), ol.oracle_decompress(w, nx, ny, nz).view(np.uint32)), (shape, scale, local)
 
 
 @pytest.mark.parametrize("shape", [(64, 64, 64), (128, 128, 128), (256, 256, 256), (256, 16, 8)], ids=lambda s: "%dx%dx%d" % s)
