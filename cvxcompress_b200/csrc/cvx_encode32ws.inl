@@ -49,8 +49,6 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
     constexpr bool EXACT = false;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
-    uint32_t* s_nzm = reinterpret_cast<uint32_t*>(smem_raw + F32_OFF_NZM);
-    int* s_base = reinterpret_cast<int*>(smem_raw + F32_OFF_BASE);
     uint2* s_lists = reinterpret_cast<uint2*>(smem_raw + E32_OFF_LIST);
     unsigned char* s_stage = smem_raw + E32_OFF_STAGE;
     __shared__ uint64_t s_bar[1];                    // the block's four TMA boxes complete one barrier phase
@@ -60,12 +58,9 @@ __global__ void __launch_bounds__(E32_T, 1) k_encode32ws(const __grid_constant__
     __shared__ unsigned long long s_off;
     __shared__ unsigned long long s_lb[E32_CT / 32 + 2];
     __shared__ int s_chunk[F32_LCAP / 32];
-    __shared__ unsigned short s_dq[F32_ROWS];
-    __shared__ int s_dqn;
     __shared__ E32Msg s_msg[2];
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const unsigned lt = (1u << lane) - 1u;
     const float gmul = p.use_local ? 1.0f : *p.glob_mulfac;
 
     auto issue_load = [&](unsigned int t) {      // one thread: TMA of block t into the block buffer, 4 boxes of 32x32x8
