@@ -1,12 +1,12 @@
 #!/usr/bin/env python
 """SASS evidence for the Blackwell-specific claims of DESIGN.md, reproducible from the repo (no GPU needed):
-per kernel of cvxcompress_b200/lib/libcvxcompress.so, the count of the instructions that prove TMA loads (UTMALDG),
+per kernel of cvxcompress_b200/lib/libcvxcompress.so, the count of the instructions that prove TMA loads (UTMALDG), bulk copies (UBLKCP),
 mbarrier waits (SYNCS), packed fp32 arithmetic (FFMA2 / FADD2 / FMUL2), cp.async (LDGSTS), named barriers (BAR),
 warp votes and shuffles; plus registers and spills from the ptxas log.   python tools/sass_summary.py > profiles/rNN_sass_summary.txt"""
 import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "cvxcompress_b200", "lib", "libcvxcompress.so")
-ops = ["UTMALDG", "SYNCS", "FFMA2", "FADD2", "FMUL2", "FFMA", "FADD", "LDGSTS", "LDS", "STS", "LDG", "STG", "BAR", "VOTE", "SHFL", "ATOMG", "REDUX"]
+ops = ["UTMALDG", "UBLKCP", "SYNCS", "FFMA2", "FADD2", "FMUL2", "FFMA", "FADD", "LDGSTS", "LDS", "STS", "LDG", "STG", "BAR", "VOTE", "SHFL", "ATOMG", "REDUX"]
 txt = subprocess.run(["cuobjdump", "-sass", lib], stdout=subprocess.PIPE, text=True).stdout
 cur, table = None, collections.OrderedDict()
 for ln in txt.splitlines():
