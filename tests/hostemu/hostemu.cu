@@ -205,3 +205,38 @@ extern "C" int emu_rle_decode8(float mulfac, float* vals, int num, const uint8_t
 
 extern "C" int emu_token_len(int b) { return token_len((uint32_t)(b & 0xFF)); }
 extern "C" int emu_quantise(float f) { return quantise(f); }
+
+// The 32^3 LIFTING encoders' arithmetic (cvx_fused32.cuh, "LIFTING encoders"): passes in the order z, y, x, bare lifting steps on
+// the z and y lines, and the x rows' multiply carrying the scalings of all three axes (fwd_lift_pair_rs with the row factors of
+// f32_row_factors).  In: a dense 32^3 block, natural order.  Out: coefficients in sub-band order (what the oracle's forward
+// transform leaves), so the caller can compare the two within the LIFTING tolerance.
+extern "C" int emu_encode32_lifting_zyx(float* b)
+{
+    constexpr int N = 32;
+    auto at = [&](int x, int y, int z) -> float& { return b[((long)z * N + y) * N + x]; };
+    float v[N];
+    // z lines, then y lines: bare lifting steps, results stored by sub-band index (reg_to_sub) as the kernels do
+    for (int y = 0; y < N; ++y)
+        for (int x = 0; x < N; ++x) {
+            for (int z = 0; z < N; ++z) v[z] = at(x, y, z);
+            fwd_lift_levels<N, 1>(v);
+            for (int r = 0; r < N; ++r) at(x, y, reg_to_sub<N, false>(r)) = v[r];
+        }
+    for (int z = 0; z < N; ++z)
+        for (int x = 0; x < N; ++x) {
+            for (int y = 0; y < N; ++y) v[y] = at(x, y, z);
+            fwd_lift_levels<N, 1>(v);
+            for (int r = 0; r < N; ++r) at(x, reg_to_sub<N, false>(r), z) = v[r];
+        }
+    // x rows in pairs (row (y, z) and row (y, z + 16), as one thread holds them), scalings of y and z folded in
+    for (int z = 0; z < 16; ++z)
+        for (int y = 0; y < N; ++y) {
+            float a[N], c[N], oa[N], oc[N];
+            for (int x = 0; x < N; ++x) { a[x] = at(x, y, z); c[x] = at(x, y, z + 16); }
+            const float sy = lift_scale_of_sub<N, true>(y);
+            const float fa = sy * lift_scale_of_sub<N, true>(z), fc = sy * lift_scale_of_sub<N, true>(z + 16);
+            fwd_lift_pair_rs<N>(a, c, oa, oc, fa, fc);
+            for (int x = 0; x < N; ++x) { at(x, y, z) = oa[sub_to_reg<N, false>(x)]; at(x, y, z + 16) = oc[sub_to_reg<N, false>(x)]; }
+        }
+    return 0;
+}

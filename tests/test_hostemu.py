@@ -38,6 +38,7 @@ def emu():
     L.emu_rle_decode.argtypes = [C.c_float, _f32p, C.c_int, C.c_void_p, C.c_long, C.c_long, C.c_int]
     L.emu_rle_decode8.argtypes = [C.c_float, _f32p, C.c_int, C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_long]
     L.emu_quantise.argtypes = [C.c_float]
+    L.emu_encode32_lifting_zyx.argtypes = [_f32p]
     return L
 
 
@@ -140,3 +141,17 @@ def test_quantise_matches_oracle(emu):
     for f in [0.0, 0.99, -0.99, 1.0, -1.5, 124.9, 125.0, 2147483520.0, 2147483648.0, -2147483648.0, -2147483904.0,
               float("nan"), float("inf"), float("-inf"), 3e9, -3e9, 8388607.5]:
         assert emu.emu_quantise(np.float32(f)) == ol.oracle().cvxo_quantise(np.float32(f)), f
+
+
+def test_encoders_zyx_order_with_folded_scalings_within_lifting_tolerance(emu):
+    """What k_encode32ws / k_encode32<LIFTING> compute -- passes z, y, x, bare lifting steps on the z and y lines, one multiply
+    on the x rows carrying all three axes' scalings -- against the oracle's forward transform (reference order x, y, z, direct
+    form): rms-relative <= 1e-6 and max-norm <= 2e-6 * max|c|, the LIFTING contract of DESIGN.md section 5."""
+    for seed in (3, 4):
+        blk = synth.g3(32768, seed=seed, lo=-1.0, hi=1.0)
+        a = blk.copy(); b = blk.copy()
+        assert emu.emu_encode32_lifting_zyx(a) == 0
+        ol.oracle().cvxo_wavelet_forward(b, 32, 32, 32, 1)
+        d = a.astype(np.float64) - b.astype(np.float64)
+        assert np.sqrt(np.mean(d * d)) <= 1e-6 * np.sqrt(np.mean(b.astype(np.float64) ** 2))
+        assert np.max(np.abs(d)) <= 2e-6 * np.max(np.abs(b))
