@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(W32_T, 1) k_decode32ws(const DecParams pin)
         CVX_PH(1);
         f32_pass_xT<EXACT, false, W32_TT>(sm, true);
         __syncwarp();
-        f32_pass_yT<EXACT, false, W32_TT>(sm);
+        f32_pass_yT<EXACT, false, W32_TT>(sm);                      // (skewing this pass as well was measured: no change)
         TBar::sync();
         CVX_PH(2);
         typename LineOf<EXACT, W32_TT>::type v[32];

@@ -19,7 +19,7 @@
         f32_pass_z2_fwd<EXACT>(sm, true);
         ETBar::sync();
         CVX_PH(1);
-        f32_pass_y2<EXACT, true>(sm);
+        f32_pass_y2<EXACT, true>(sm, true);      // skewed halves: one half's loads / stores overlap the other's math
         __syncwarp();                    // warp w owns the y lines and the x rows of z slices w and w + 16
         CVX_PH(2);
         float w[2][32];                  // coefficients of rows tid and tid + 512: w[h][sub_to_reg(x)]

@@ -178,17 +178,20 @@ __device__ __forceinline__ void f32_pass_y(float* sm)
 
 // y lines, two per thread side by side in packed registers: lines (x = lane, z = warp) and (x, z + 16) are
 // 16384 floats apart with the same swizzle, so both come from the same eight base pointers (FADD2/FFMA2 math)
+// `skew` as in f32_pass_x: the second half of a 512-thread group starts its loads when the first half's are issued
 template <bool EXACT, bool FWD>
-__device__ __forceinline__ void f32_pass_y2(float* sm)
+__device__ __forceinline__ void f32_pass_y2(float* sm, const bool skew = false)
 {
     const int x = threadIdx.x & 31, z = threadIdx.x >> 5;
     float* a[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = sm + z * 1024 + (x ^ (k << 2));
     typename PairOf<EXACT>::type v[32];
+    if (skew && (threadIdx.x & 256)) asm volatile("bar.sync 7, 512;" ::: "memory");
     if (FWD) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) p_set(v[j], a[j & 7][j * 32], a[j & 7][j * 32 + 16384]);
+        if (skew && !(threadIdx.x & 256)) asm volatile("bar.arrive 7, 512;" ::: "memory");
         f32_line_yz<EXACT, true>(v);
 #pragma unroll
         for (int r = 0; r < 32; ++r) {
@@ -202,6 +205,7 @@ __device__ __forceinline__ void f32_pass_y2(float* sm)
             const int s = reg_to_sub<32, EXACT>(r);
             p_set(v[r], a[s & 7][s * 32], a[s & 7][s * 32 + 16384]);
         }
+        if (skew && !(threadIdx.x & 256)) asm volatile("bar.arrive 7, 512;" ::: "memory");
         f32_line_yz<EXACT, false>(v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -244,10 +248,10 @@ __device__ __forceinline__ void f32_pass_xT(float* sm, const bool skew = false)
     }
 }
 template <bool EXACT, bool FWD, int T>
-__device__ __forceinline__ void f32_pass_yT(float* sm)
+__device__ __forceinline__ void f32_pass_yT(float* sm, const bool skew = false)
 {
     if constexpr (T == 512) {
-        f32_pass_y2<EXACT, FWD>(sm);
+        f32_pass_y2<EXACT, FWD>(sm, skew);
     } else {
         const int x = threadIdx.x & 31, z = threadIdx.x >> 5;
         float* a[8];
